@@ -1,0 +1,137 @@
+/* nbody_gpu.h -- C ABI of the B200 all-pairs N-body step (libnbody_gpu.so).
+ *
+ * The reference (jfdev001/parallel-nbody) has no plugin or FFI interface: its
+ * boundary is the four static calls in the step loop,
+ *     clear_forces / compute_forces / compute_velocities / compute_positions
+ *     + MPI_Allgatherv + slot flip
+ * (nbody/nbody-seq.c:457-464, nbody/nbody-par.c:901-921), all mutating one
+ * `struct world *` in place.  This header is the boundary a maintainer would bind
+ * instead: plain pointers and sizes, no CUDA or torch types.  Every pointer is
+ * host memory owned by the caller unless stated otherwise; the library copies.
+ *
+ * Return value: 0 = ok, nonzero = failure (NBODY_GPU_E*); the message is in
+ * nbody_gpu_last_error().  The reference's error behaviour is fprintf(stderr)+
+ * exit(1) (nbody-seq.c:401-404,431-434); the host driver does exactly that with
+ * the message.  There is no CPU fallback anywhere behind this interface: without
+ * a CUDA device nbody_gpu_init fails.
+ *
+ * Threading: one host thread drives a handle (the reference's step loop has one
+ * caller thread per rank).  nbody_gpu_step only enqueues; fetch/sync wait.
+ */
+#ifndef NBODY_GPU_H
+#define NBODY_GPU_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NBODY_GPU_ABI_VERSION 1
+
+enum {
+    NBODY_GPU_OK = 0,
+    NBODY_GPU_EINVAL = 1,   /* bad argument */
+    NBODY_GPU_ECUDA = 2,    /* CUDA runtime error (no device, launch failure, ...) */
+    NBODY_GPU_ENCCL = 3,    /* NCCL missing or failed */
+    NBODY_GPU_ENOMEM = 4
+};
+
+enum {
+    NBODY_GPU_MODE_EXACT = 0,  /* no FMA contraction, detmath trig, reference summation order:
+                                  bit-identical to nbody-seq.c linked against include/nbody_detmath.h */
+    NBODY_GPU_MODE_FAST = 1    /* FMA, algebraic force direction, j-range split into fixed chunks */
+};
+
+#define NBODY_GPU_NCCL_ID_BYTES 128
+
+typedef struct nbody_gpu nbody_gpu;   /* opaque, owned by the library */
+
+/* Replaces: struct world's scalar members (nbody-seq.c:42-50) + the MPI rank/size
+ * pair (nbody-par.c:775-780).  Zero-initialise, then set what you need. */
+typedef struct nbody_gpu_cfg {
+    int n;          /* bodies (world->bodyCt); >= 1, no MAXBODIES cap */
+    int xdim;       /* world->xdim (from the P6 header, nbody-seq.c:276) */
+    int ydim;       /* world->ydim */
+    int mode;       /* NBODY_GPU_MODE_* */
+    int ngpus;      /* single-process sharding over devices 0..ngpus-1; <= 1 means one device */
+    int device;     /* device ordinal when ngpus <= 1; -1 = current device */
+    /* One process per GPU (the nbody-par MPI shape): rank/nranks as MPI_Comm_rank/size,
+     * nccl_id = NBODY_GPU_NCCL_ID_BYTES bytes obtained from nbody_gpu_nccl_unique_id()
+     * on rank 0 and distributed by the caller (MPI_Bcast, torch.distributed, ...).
+     * nranks <= 1 disables it.  Mutually exclusive with ngpus > 1. */
+    int rank;
+    int nranks;
+    const void *nccl_id;
+    int jsplit;     /* fast mode: number of fixed j-chunks (0 = library default for n) */
+    int use_graph;  /* 1 = capture the step loop in a CUDA graph (default when 0: yes), -1 = plain launches */
+    int fused;      /* 1 = integrate inside the force kernel's epilogue where possible; 0 = default; -1 = never */
+} nbody_gpu_cfg;
+
+/* Replaces calloc(world) + initialize_simulation_data + MPI_Bcast
+ * (nbody-par.c:810,870-874): creates device state from the six initial arrays
+ * (length n each).  Forces start at zero like the reference's calloc. */
+int nbody_gpu_init(nbody_gpu **out, const nbody_gpu_cfg *cfg,
+                   const double *x, const double *y,
+                   const double *xv, const double *yv,
+                   const double *mass, const double *radius);
+
+/* Re-upload positions and velocities into an existing handle (same n); forces are
+ * zeroed.  For harnesses that time many runs without re-creating graphs. */
+int nbody_gpu_set_state(nbody_gpu *h, const double *x, const double *y,
+                        const double *xv, const double *yv);
+
+/* Replaces the body of the step loop, `steps` times (nbody-seq.c:457-464;
+ * nbody-par.c:901-921 including MPI_Allgatherv and old ^= 1).  Asynchronous. */
+int nbody_gpu_step(nbody_gpu *h, int steps);
+
+/* As nbody_gpu_step, but bracketed by CUDA events on the library's own stream(s) and
+ * synchronised; *ms receives the device time (max over this handle's devices). */
+int nbody_gpu_step_timed(nbody_gpu *h, int steps, float *ms);
+
+/* compute_forces only (clear_forces + compute_forces, nbody-seq.c:458-459) on the
+ * current positions; state is otherwise untouched.  Synchronous. */
+int nbody_gpu_forces(nbody_gpu *h, double *xf, double *yf);
+
+/* Replaces reading world->bodies after the loop (print(), nbody-seq.c:356-365):
+ * waits for the queue, then copies the CURRENT positions, the last step's forces and
+ * the velocities to the host (length n each; any pointer may be NULL).  In
+ * multi-rank mode every rank receives the full state, like the reference after its
+ * last MPI_Allgatherv (nbody-par.c:933-936). */
+int nbody_gpu_fetch(nbody_gpu *h, double *x, double *y, double *xf, double *yf,
+                    double *xv, double *yv);
+
+int nbody_gpu_sync(nbody_gpu *h);
+void nbody_gpu_destroy(nbody_gpu *h);
+
+/* Thread-local message of the last failure on this thread ("" if none). */
+const char *nbody_gpu_last_error(void);
+
+/* Kernels launched through this handle so far (force, integrate, reduce and NCCL calls counted
+ * separately in out[0..3] if out != NULL); returns the total. */
+long long nbody_gpu_launch_count(const nbody_gpu *h, long long out[4]);
+
+/* Row partition used for sharding: rank r owns rows [lo, hi).  Equal ceil(n/P) blocks
+ * (the last ones may be short or empty) so that one ncclAllGather replaces
+ * MPI_Allgatherv (nbody-par.c:913-917). */
+void nbody_gpu_partition(int n, int nranks, int rank, int *lo, int *hi);
+
+/* The reference's own partition rule, for comparison (nbody-par.c:225-263):
+ * counts n/P, ranks 1..n%P get one more; displacements are the prefix sum. */
+void nbody_gpu_partition_reference(int n, int nranks, int *counts, int *displs);
+
+/* ncclGetUniqueId through the library's NCCL binding; out = NBODY_GPU_NCCL_ID_BYTES bytes. */
+int nbody_gpu_nccl_unique_id(void *out);
+
+/* Number of visible CUDA devices (0 if none / no driver). */
+int nbody_gpu_device_count(void);
+
+/* Measured FP64 (non-tensor) peak of `device`: a dependent-chain-free DFMA kernel,
+ * `ms_budget` milliseconds long; *tflops = 2 * DFMA/s / 1e12, *sm_mhz_est = the SM clock
+ * implied by a clock64() bracket.  The roofline denominator of bench.py. */
+int nbody_gpu_fp64_peak(int device, int ms_budget, double *tflops, double *sm_mhz_est);
+
+int nbody_gpu_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NBODY_GPU_H */

@@ -1,0 +1,177 @@
+"""parallel-nbody_b200 -- host-side Python mirror of the C ABI in include/nbody_gpu.h.
+
+The product is libnbody_gpu.so (hand-written sm_100a CUDA behind a C ABI); this module is a
+thin ctypes binding used by tests/, bench.py and __graft_entry__.py.  It adds no arithmetic
+of its own and has no fallback: if the library is missing or no CUDA device is usable, the
+calls raise.
+
+Reference mapping (jfdev001/parallel-nbody): NBodyGPU(...) ~ calloc(world) + initialize +
+MPI_Bcast (nbody/nbody-par.c:810,870-874); .step(k) ~ the step loop (nbody-par.c:901-921);
+.fetch() ~ reading world->bodies for print() (nbody-par.c:740-750).
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libnbody_gpu.so")
+
+MODE_EXACT = 0
+MODE_FAST = 1
+NCCL_ID_BYTES = 128
+
+_dp = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+
+
+class NBodyGPUError(RuntimeError):
+    pass
+
+
+class _Cfg(ctypes.Structure):
+    _fields_ = [("n", ctypes.c_int), ("xdim", ctypes.c_int), ("ydim", ctypes.c_int),
+                ("mode", ctypes.c_int), ("ngpus", ctypes.c_int), ("device", ctypes.c_int),
+                ("rank", ctypes.c_int), ("nranks", ctypes.c_int), ("nccl_id", ctypes.c_void_p),
+                ("jsplit", ctypes.c_int), ("use_graph", ctypes.c_int), ("fused", ctypes.c_int)]
+
+
+_lib = None
+
+
+def build():
+    """Compile libnbody_gpu.so in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    import subprocess
+    subprocess.run(["make", "-C", os.path.join(_HERE, "csrc"), "--no-print-directory"], check=True)
+
+
+def lib():
+    """Load libnbody_gpu.so; raises NBodyGPUError if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise NBodyGPUError("libnbody_gpu.so is not built (run `make -C parallel-nbody_b200/csrc` "
+                            "or __graft_entry__.build()); there is no CPU fallback")
+    L = ctypes.CDLL(LIB_PATH)
+    vp, ci = ctypes.c_void_p, ctypes.c_int
+    odp = ctypes.c_void_p  # optional double* (may be NULL)
+    L.nbody_gpu_init.argtypes = [ctypes.POINTER(vp), ctypes.POINTER(_Cfg)] + [_dp] * 6
+    L.nbody_gpu_set_state.argtypes = [vp] + [_dp] * 4
+    L.nbody_gpu_step.argtypes = [vp, ci]
+    L.nbody_gpu_step_timed.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_float)]
+    L.nbody_gpu_forces.argtypes = [vp, _dp, _dp]
+    L.nbody_gpu_fetch.argtypes = [vp] + [odp] * 6
+    L.nbody_gpu_sync.argtypes = [vp]
+    L.nbody_gpu_destroy.argtypes = [vp]
+    L.nbody_gpu_destroy.restype = None
+    L.nbody_gpu_last_error.restype = ctypes.c_char_p
+    L.nbody_gpu_launch_count.argtypes = [vp, ctypes.POINTER(ctypes.c_longlong)]
+    L.nbody_gpu_launch_count.restype = ctypes.c_longlong
+    L.nbody_gpu_partition.argtypes = [ci, ci, ci, ctypes.POINTER(ci), ctypes.POINTER(ci)]
+    L.nbody_gpu_partition.restype = None
+    L.nbody_gpu_partition_reference.argtypes = [ci, ci, ctypes.POINTER(ci), ctypes.POINTER(ci)]
+    L.nbody_gpu_partition_reference.restype = None
+    L.nbody_gpu_nccl_unique_id.argtypes = [ctypes.c_char_p]
+    L.nbody_gpu_device_count.restype = ci
+    L.nbody_gpu_fp64_peak.argtypes = [ci, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
+    L.nbody_gpu_abi_version.restype = ci
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc != 0:
+        raise NBodyGPUError("nbody_gpu error %d: %s" % (rc, lib().nbody_gpu_last_error().decode()))
+
+
+def device_count():
+    return lib().nbody_gpu_device_count()
+
+
+def nccl_unique_id():
+    buf = ctypes.create_string_buffer(NCCL_ID_BYTES)
+    _check(lib().nbody_gpu_nccl_unique_id(buf))
+    return buf.raw
+
+
+def partition(n, nranks, rank):
+    lo, hi = ctypes.c_int(), ctypes.c_int()
+    lib().nbody_gpu_partition(n, nranks, rank, ctypes.byref(lo), ctypes.byref(hi))
+    return lo.value, hi.value
+
+
+def partition_reference(n, nranks):
+    counts = (ctypes.c_int * nranks)()
+    displs = (ctypes.c_int * nranks)()
+    lib().nbody_gpu_partition_reference(n, nranks, counts, displs)
+    return list(counts), list(displs)
+
+
+def fp64_peak(device=-1, ms_budget=200):
+    """Measured FP64 DFMA peak of the device: (TFLOP/s, implied SM MHz)."""
+    tf, mhz = ctypes.c_double(), ctypes.c_double()
+    _check(lib().nbody_gpu_fp64_peak(device, ms_budget, ctypes.byref(tf), ctypes.byref(mhz)))
+    return tf.value, mhz.value
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+class NBodyGPU:
+    """One N-body world on the GPU(s). Arrays are host numpy float64 of length n."""
+
+    def __init__(self, x, y, xv, yv, mass, radius, xdim=1024, ydim=768, mode=MODE_EXACT,
+                 ngpus=1, device=-1, rank=0, nranks=1, nccl_id=None, jsplit=0, use_graph=0, fused=0):
+        x, y, xv, yv, mass, radius = map(_f64, (x, y, xv, yv, mass, radius))
+        self.n = int(x.shape[0])
+        for a in (y, xv, yv, mass, radius):
+            if a.shape != (self.n,):
+                raise ValueError("all body arrays must have the same length")
+        self._id = ctypes.create_string_buffer(nccl_id, NCCL_ID_BYTES) if nccl_id else None
+        cfg = _Cfg(self.n, xdim, ydim, mode, ngpus, device, rank, nranks,
+                   ctypes.cast(self._id, ctypes.c_void_p) if self._id else None, jsplit, use_graph, fused)
+        self._h = ctypes.c_void_p()
+        _check(lib().nbody_gpu_init(ctypes.byref(self._h), ctypes.byref(cfg), x, y, xv, yv, mass, radius))
+
+    def set_state(self, x, y, xv, yv):
+        _check(lib().nbody_gpu_set_state(self._h, _f64(x), _f64(y), _f64(xv), _f64(yv)))
+
+    def step(self, steps=1):
+        _check(lib().nbody_gpu_step(self._h, int(steps)))
+
+    def step_timed(self, steps=1):
+        """Run `steps` steps bracketed by CUDA events on the library's stream; returns milliseconds."""
+        ms = ctypes.c_float()
+        _check(lib().nbody_gpu_step_timed(self._h, int(steps), ctypes.byref(ms)))
+        return ms.value
+
+    def forces(self):
+        xf, yf = np.empty(self.n), np.empty(self.n)
+        _check(lib().nbody_gpu_forces(self._h, xf, yf))
+        return xf, yf
+
+    def fetch(self):
+        """(x, y, xf, yf, xv, yv): the six columns the reference's print() shows."""
+        out = [np.empty(self.n) for _ in range(6)]
+        _check(lib().nbody_gpu_fetch(self._h, *[a.ctypes.data_as(ctypes.c_void_p) for a in out]))
+        return tuple(out)
+
+    def sync(self):
+        _check(lib().nbody_gpu_sync(self._h))
+
+    def launch_count(self):
+        out = (ctypes.c_longlong * 4)()
+        total = lib().nbody_gpu_launch_count(self._h, out)
+        return total, list(out)
+
+    def close(self):
+        if self._h:
+            lib().nbody_gpu_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,23 @@
+// kernels_exact.cu -- EXACT-mode instantiations.  Build with -fmad=false (see Makefile):
+// bit-identical to reference nbody-seq.c compiled without FMA contraction and linked
+// against include/nbody_detmath.h (oracle/_ref/nbody-seq-det-hex).
+#include "step_kernels.cuh"
+
+namespace nbody {
+
+void launch_forces_exact(const ForceArgs &a, cudaStream_t st)
+{
+    const int rows = a.hi - a.lo;
+    if (rows <= 0) return;
+    dim3 grid((rows + FORCE_THREADS - 1) / FORCE_THREADS, 1);
+    forces_kernel<MODE_EXACT><<<grid, FORCE_THREADS, 0, st>>>(a);
+}
+
+void launch_integrate_exact(const IntegrateArgs &a, cudaStream_t st)
+{
+    const int rows = a.hi - a.lo;
+    if (rows <= 0) return;
+    integrate_kernel<MODE_EXACT><<<(rows + 127) / 128, 128, 0, st>>>(a);
+}
+
+}  // namespace nbody

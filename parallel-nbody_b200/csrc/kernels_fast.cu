@@ -1,0 +1,28 @@
+// kernels_fast.cu -- FAST-mode instantiations (FMA contraction on, algebraic force direction).
+#include "step_kernels.cuh"
+
+namespace nbody {
+
+void launch_forces_fast(const ForceArgs &a, int nsplit, cudaStream_t st)
+{
+    const int rows = a.hi - a.lo;
+    if (rows <= 0) return;
+    dim3 grid((rows + FORCE_THREADS - 1) / FORCE_THREADS, nsplit);
+    forces_kernel<MODE_FAST><<<grid, FORCE_THREADS, 0, st>>>(a);
+}
+
+void launch_integrate_fast(const IntegrateArgs &a, cudaStream_t st)
+{
+    const int rows = a.hi - a.lo;
+    if (rows <= 0) return;
+    integrate_kernel<MODE_FAST><<<(rows + 127) / 128, 128, 0, st>>>(a);
+}
+
+void launch_reduce_fast(const IntegrateArgs &a, cudaStream_t st)
+{
+    const int rows = a.hi - a.lo;
+    if (rows <= 0) return;
+    reduce_partials_kernel<MODE_FAST><<<(rows + 127) / 128, 128, 0, st>>>(a);
+}
+
+}  // namespace nbody

@@ -1,0 +1,570 @@
+// nbody_gpu.cu -- implementation of the C ABI in include/nbody_gpu.h.
+//
+// One handle drives either one device, several devices of one process (row shards,
+// ncclCommInitAll), or one rank of a multi-process job (row shard, ncclCommInitRank).
+// Per step and per device:  forces_kernel -> integrate_kernel -> all-gather of the new
+// positions (only when sharded).  Single-device step loops are captured in a CUDA graph.
+// There is no CPU fallback: every entry point that computes needs a CUDA device.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "../../include/nbody_gpu.h"
+#include "nccl_dl.h"
+#include "step_args.h"
+
+namespace nbody {
+
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define NB_CUDA(call)                                                                              \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(NBODY_GPU_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_),   \
+                        __FILE__, __LINE__);                                                       \
+    } while (0)
+
+#define NB_NCCL(api, call)                                                                         \
+    do {                                                                                           \
+        int r_ = (call);                                                                           \
+        if (r_ != NCCL_SUCCESS)                                                                    \
+            return fail(NBODY_GPU_ENCCL, "%s failed: %s (%s:%d)", #call, (api)->GetErrorString(r_), \
+                        __FILE__, __LINE__);                                                       \
+    } while (0)
+
+struct Shard {
+    int device = 0;
+    int lo = 0, hi = 0;          // rows owned
+    int part_index = 0;          // position of this shard in the all-gather (rank)
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    double2 *pos[2] = {nullptr, nullptr};
+    double2 *mr = nullptr;
+    double2 *vel = nullptr;
+    double2 *frc = nullptr;
+    double2 *part = nullptr;
+    NcclComm comm = nullptr;
+    cudaGraphExec_t graph[2] = {nullptr, nullptr};   // indexed by the starting slot
+};
+
+}  // namespace nbody
+
+using namespace nbody;
+
+struct nbody_gpu {
+    nbody_gpu_cfg cfg;
+    int n = 0;
+    int nshards_total = 1;       // P: shards across the whole job
+    int rows_per_shard = 0;      // ceil(n / P)
+    int npad = 0;                // P * rows_per_shard (leading dimension of every array)
+    int nsplit = 1;              // fast mode: j-chunks
+    int chunk = 0;               // fast mode: j-chunk length
+    int cur = 0;                 // slot holding the current positions (the reference's world->old)
+    int graph_steps = 0;         // steps captured per graph launch (even), 0 = graphs off
+    bool sharded = false;
+    std::vector<Shard> shards;   // local shards (1, or ngpus in single-process mode)
+    double2 *stage = nullptr;    // pinned host staging, npad elements
+    long long launches[4] = {0, 0, 0, 0};   // force, integrate, reduce, nccl
+};
+
+namespace nbody {
+
+static void partition(int n, int nranks, int rank, int *lo, int *hi)
+{
+    if (nranks < 1) nranks = 1;
+    const int rows = (n + nranks - 1) / nranks;
+    long long l = static_cast<long long>(rank) * rows;
+    long long h = l + rows;
+    if (l > n) l = n;
+    if (h > n) h = n;
+    *lo = static_cast<int>(l);
+    *hi = static_cast<int>(h);
+}
+
+// Fast mode: number of fixed j-chunks, a function of n only so that results do not
+// depend on how many GPUs share the rows.
+static void choose_split(int n, int requested, int *nsplit, int *chunk)
+{
+    int s = requested;
+    if (s <= 0) {
+        const long long want = (2664LL * 1024 + n - 1) / n;   // >= ~18 CTAs per SM on an 8-way shard
+        s = 8;
+        while (s < want && s < 64) s *= 2;
+        while (s > 1 && n / s < 1024) s /= 2;
+    }
+    if (s > n) s = n;
+    if (s < 1) s = 1;
+    int c = (n + s - 1) / s;
+    c = (c + TILE_J - 1) / TILE_J * TILE_J;
+    *chunk = c;
+    *nsplit = (n + c - 1) / c;
+}
+
+static void free_shard(Shard &s)
+{
+    cudaSetDevice(s.device);
+    for (int k = 0; k < 2; ++k) {
+        if (s.graph[k]) cudaGraphExecDestroy(s.graph[k]);
+        if (s.pos[k]) cudaFree(s.pos[k]);
+    }
+    if (s.mr) cudaFree(s.mr);
+    if (s.vel) cudaFree(s.vel);
+    if (s.frc) cudaFree(s.frc);
+    if (s.part) cudaFree(s.part);
+    if (s.ev0) cudaEventDestroy(s.ev0);
+    if (s.ev1) cudaEventDestroy(s.ev1);
+    if (s.comm) {
+        const NcclApi *api = nccl_api(nullptr);
+        if (api) api->CommDestroy(s.comm);
+    }
+    if (s.stream) cudaStreamDestroy(s.stream);
+    s = Shard();
+}
+
+static ForceArgs force_args(const nbody_gpu *h, const Shard &s, int slot)
+{
+    ForceArgs a;
+    a.pos = s.pos[slot];
+    a.mr = s.mr;
+    a.out = (h->cfg.mode == NBODY_GPU_MODE_FAST) ? s.part : s.frc;
+    a.n = h->n;
+    a.npad = h->npad;
+    a.lo = s.lo;
+    a.hi = s.hi;
+    a.chunk = h->chunk;
+    return a;
+}
+
+static IntegrateArgs integrate_args(const nbody_gpu *h, const Shard &s, int slot)
+{
+    IntegrateArgs a;
+    a.pos_old = s.pos[slot];
+    a.pos_new = s.pos[slot ^ 1];
+    a.mr = s.mr;
+    a.vel = s.vel;
+    a.frc = s.frc;
+    a.part = s.part;
+    a.nsplit = h->nsplit;
+    a.npad = h->npad;
+    a.lo = s.lo;
+    a.hi = s.hi;
+    a.xdim = h->cfg.xdim;
+    a.ydim = h->cfg.ydim;
+    return a;
+}
+
+// Enqueue the two kernels of one step on shard s, reading slot `slot`.
+static void enqueue_step_kernels(nbody_gpu *h, Shard &s, int slot)
+{
+    if (h->cfg.mode == NBODY_GPU_MODE_FAST) {
+        launch_forces_fast(force_args(h, s, slot), h->nsplit, s.stream);
+        launch_integrate_fast(integrate_args(h, s, slot), s.stream);
+    } else {
+        launch_forces_exact(force_args(h, s, slot), s.stream);
+        launch_integrate_exact(integrate_args(h, s, slot), s.stream);
+    }
+}
+
+}  // namespace nbody
+
+namespace nbody {
+
+// In-place all-gather of `buf` (npad double2, shard r's rows at [r*rows_per_shard, ...)) on every
+// local shard: replaces MPI_Allgatherv (reference nbody-par.c:913-917).
+static int allgather(nbody_gpu *h, int which /*0,1 = pos slot, 2 = vel, 3 = frc*/)
+{
+    if (!h->sharded) return NBODY_GPU_OK;
+    const char *why = "";
+    const NcclApi *api = nccl_api(&why);
+    if (!api) return fail(NBODY_GPU_ENCCL, "NCCL unavailable: %s", why);
+    const size_t count = static_cast<size_t>(h->rows_per_shard) * 2;   // doubles per shard
+    const bool group = h->shards.size() > 1;
+    if (group) NB_NCCL(api, api->GroupStart());
+    for (Shard &s : h->shards) {
+        double2 *buf = which == 0 ? s.pos[0] : which == 1 ? s.pos[1] : which == 2 ? s.vel : s.frc;
+        const double2 *send = buf + static_cast<size_t>(s.part_index) * h->rows_per_shard;
+        NB_NCCL(api, api->AllGather(send, buf, count, NCCL_DOUBLE, s.comm, s.stream));
+    }
+    if (group) NB_NCCL(api, api->GroupEnd());
+    h->launches[3] += static_cast<long long>(h->shards.size());
+    return NBODY_GPU_OK;
+}
+
+static int upload(nbody_gpu *h, double2 *Shard::*field, int slot, const double *a, const double *b)
+{
+    // interleave on the host into pinned staging, then one H2D copy per local device
+    for (int i = 0; i < h->n; ++i) h->stage[i] = make_double2(a ? a[i] : 0.0, b ? b[i] : 0.0);
+    for (int i = h->n; i < h->npad; ++i) h->stage[i] = make_double2(0.0, 0.0);
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        double2 *dst = field ? s.*field : s.pos[slot];
+        NB_CUDA(cudaMemcpyAsync(dst, h->stage, sizeof(double2) * h->npad, cudaMemcpyHostToDevice, s.stream));
+        NB_CUDA(cudaStreamSynchronize(s.stream));   // staging buffer is reused
+    }
+    return NBODY_GPU_OK;
+}
+
+static int build_graph(nbody_gpu *h, Shard &s, int start_slot)
+{
+    cudaGraph_t g = nullptr;
+    NB_CUDA(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
+    int slot = start_slot;
+    for (int k = 0; k < h->graph_steps; ++k) {
+        enqueue_step_kernels(h, s, slot);
+        slot ^= 1;
+    }
+    cudaError_t e = cudaStreamEndCapture(s.stream, &g);
+    if (e != cudaSuccess) return fail(NBODY_GPU_ECUDA, "graph capture failed: %s", cudaGetErrorString(e));
+    e = cudaGraphInstantiate(&s.graph[start_slot], g, 0);
+    cudaGraphDestroy(g);
+    if (e != cudaSuccess) return fail(NBODY_GPU_ECUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(e));
+    return NBODY_GPU_OK;
+}
+
+static int sync_all(nbody_gpu *h)
+{
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        NB_CUDA(cudaStreamSynchronize(s.stream));
+    }
+    return NBODY_GPU_OK;
+}
+
+static int do_steps(nbody_gpu *h, int steps)
+{
+    if (steps < 0) return fail(NBODY_GPU_EINVAL, "steps must be >= 0");
+    int left = steps;
+    if (!h->sharded && h->graph_steps > 0) {
+        Shard &s = h->shards[0];
+        NB_CUDA(cudaSetDevice(s.device));
+        while (left >= h->graph_steps) {
+            if (!s.graph[h->cur]) {
+                int rc = build_graph(h, s, h->cur);
+                if (rc) return rc;
+            }
+            NB_CUDA(cudaGraphLaunch(s.graph[h->cur], s.stream));
+            h->launches[0] += h->graph_steps;
+            h->launches[1] += h->graph_steps;
+            left -= h->graph_steps;   // graph_steps is even: h->cur is unchanged
+        }
+    }
+    for (; left > 0; --left) {
+        for (Shard &s : h->shards) {
+            NB_CUDA(cudaSetDevice(s.device));
+            enqueue_step_kernels(h, s, h->cur);
+        }
+        h->launches[0] += static_cast<long long>(h->shards.size());
+        h->launches[1] += static_cast<long long>(h->shards.size());
+        int rc = allgather(h, h->cur ^ 1);
+        if (rc) return rc;
+        h->cur ^= 1;   // the reference's world->old ^= 1 (nbody-seq.c:464)
+    }
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        NB_CUDA(cudaGetLastError());
+    }
+    return NBODY_GPU_OK;
+}
+
+}  // namespace nbody
+
+// ---------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------
+extern "C" {
+
+int nbody_gpu_abi_version(void) { return NBODY_GPU_ABI_VERSION; }
+
+const char *nbody_gpu_last_error(void) { return g_err; }
+
+int nbody_gpu_device_count(void)
+{
+    int c = 0;
+    if (cudaGetDeviceCount(&c) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return c;
+}
+
+void nbody_gpu_partition(int n, int nranks, int rank, int *lo, int *hi) { partition(n, nranks, rank, lo, hi); }
+
+void nbody_gpu_partition_reference(int n, int nranks, int *counts, int *displs)
+{
+    // nbody-par.c:225-250: n/P each, then ranks n%P down to 1 get one more (rank 0 never does)
+    if (nranks < 1) return;
+    for (int r = 0; r < nranks; ++r) counts[r] = n / nranks;
+    for (int r = n % nranks; r > 0; --r) counts[r] += 1;
+    displs[0] = 0;
+    for (int r = 1; r < nranks; ++r) displs[r] = displs[r - 1] + counts[r - 1];
+}
+
+int nbody_gpu_nccl_unique_id(void *out)
+{
+    if (!out) return fail(NBODY_GPU_EINVAL, "out is NULL");
+    const char *why = "";
+    const NcclApi *api = nccl_api(&why);
+    if (!api) return fail(NBODY_GPU_ENCCL, "NCCL unavailable: %s", why);
+    NcclUniqueId id;
+    NB_NCCL(api, api->GetUniqueId(&id));
+    memcpy(out, &id, NBODY_GPU_NCCL_ID_BYTES);
+    return NBODY_GPU_OK;
+}
+
+void nbody_gpu_destroy(nbody_gpu *h)
+{
+    if (!h) return;
+    for (Shard &s : h->shards) free_shard(s);
+    if (h->stage) cudaFreeHost(h->stage);
+    delete h;
+}
+
+static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, const double *y, const double *xv,
+                     const double *yv, const double *mass, const double *radius)
+{
+    h->cfg = *cfg;
+    h->n = cfg->n;
+    const bool multi_rank = cfg->nranks > 1;
+    const bool multi_dev = cfg->ngpus > 1;
+    if (multi_rank && multi_dev) return fail(NBODY_GPU_EINVAL, "ngpus > 1 and nranks > 1 are mutually exclusive");
+    int ndev = 0;
+    NB_CUDA(cudaGetDeviceCount(&ndev));
+    if (ndev < 1) return fail(NBODY_GPU_ECUDA, "no CUDA device");
+    const int P = multi_rank ? cfg->nranks : (multi_dev ? cfg->ngpus : 1);
+    if (multi_dev && cfg->ngpus > ndev)
+        return fail(NBODY_GPU_EINVAL, "ngpus = %d but only %d CUDA devices are visible", cfg->ngpus, ndev);
+    if (multi_rank && (cfg->rank < 0 || cfg->rank >= cfg->nranks || !cfg->nccl_id))
+        return fail(NBODY_GPU_EINVAL, "multi-rank init needs 0 <= rank < nranks and nccl_id");
+    h->nshards_total = P;
+    h->sharded = P > 1;
+    h->rows_per_shard = (h->n + P - 1) / P;
+    h->npad = h->rows_per_shard * P;
+    if (cfg->mode == NBODY_GPU_MODE_FAST) choose_split(h->n, cfg->jsplit, &h->nsplit, &h->chunk);
+    else { h->nsplit = 1; h->chunk = h->n; }
+    if (cfg->use_graph >= 0 && !h->sharded) {
+        // small worlds are launch-bound: put more steps behind one graph launch
+        h->graph_steps = (h->n <= 2048) ? 32 : (h->n <= 16384 ? 8 : 2);
+    }
+
+    const int nlocal = multi_dev ? cfg->ngpus : 1;
+    h->shards.resize(nlocal);
+    for (int k = 0; k < nlocal; ++k) {
+        Shard &s = h->shards[k];
+        if (multi_dev) s.device = k;
+        else if (cfg->device >= 0) s.device = cfg->device;
+        else NB_CUDA(cudaGetDevice(&s.device));
+        if (s.device >= ndev) return fail(NBODY_GPU_EINVAL, "device %d not visible (%d devices)", s.device, ndev);
+        s.part_index = multi_rank ? cfg->rank : k;
+        partition(h->n, P, s.part_index, &s.lo, &s.hi);
+        NB_CUDA(cudaSetDevice(s.device));
+        NB_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        NB_CUDA(cudaEventCreate(&s.ev0));
+        NB_CUDA(cudaEventCreate(&s.ev1));
+        const size_t bytes = sizeof(double2) * static_cast<size_t>(h->npad);
+        NB_CUDA(cudaMalloc(&s.pos[0], bytes));
+        NB_CUDA(cudaMalloc(&s.pos[1], bytes));
+        NB_CUDA(cudaMalloc(&s.mr, bytes));
+        NB_CUDA(cudaMalloc(&s.vel, bytes));
+        NB_CUDA(cudaMalloc(&s.frc, bytes));
+        NB_CUDA(cudaMemsetAsync(s.pos[1], 0, bytes, s.stream));
+        NB_CUDA(cudaMemsetAsync(s.frc, 0, bytes, s.stream));
+        if (cfg->mode == NBODY_GPU_MODE_FAST) {
+            NB_CUDA(cudaMalloc(&s.part, bytes * h->nsplit));
+            NB_CUDA(cudaMemsetAsync(s.part, 0, bytes * h->nsplit, s.stream));
+        }
+    }
+    NB_CUDA(cudaMallocHost(&h->stage, sizeof(double2) * static_cast<size_t>(h->npad)));
+
+    if (h->sharded) {
+        const char *why = "";
+        const NcclApi *api = nccl_api(&why);
+        if (!api) return fail(NBODY_GPU_ENCCL, "NCCL unavailable: %s", why);
+        if (multi_rank) {
+            NcclUniqueId id;
+            memcpy(&id, cfg->nccl_id, NBODY_GPU_NCCL_ID_BYTES);
+            NB_CUDA(cudaSetDevice(h->shards[0].device));
+            NB_NCCL(api, api->CommInitRank(&h->shards[0].comm, cfg->nranks, id, cfg->rank));
+        } else {
+            std::vector<NcclComm> comms(nlocal);
+            std::vector<int> devs(nlocal);
+            for (int k = 0; k < nlocal; ++k) devs[k] = h->shards[k].device;
+            NB_NCCL(api, api->CommInitAll(comms.data(), nlocal, devs.data()));
+            for (int k = 0; k < nlocal; ++k) h->shards[k].comm = comms[k];
+        }
+    }
+
+    int rc = upload(h, nullptr, 0, x, y);
+    if (!rc) rc = upload(h, &Shard::mr, 0, mass, radius);
+    if (!rc) rc = upload(h, &Shard::vel, 0, xv, yv);
+    // padding rows of mr must not be zero-radius/zero-mass hazards: they are never read (j < n)
+    h->cur = 0;
+    return rc;
+}
+
+int nbody_gpu_init(nbody_gpu **out, const nbody_gpu_cfg *cfg, const double *x, const double *y, const double *xv,
+                   const double *yv, const double *mass, const double *radius)
+{
+    g_err[0] = 0;
+    if (!out) return fail(NBODY_GPU_EINVAL, "out is NULL");
+    *out = nullptr;
+    if (!cfg || !x || !y || !xv || !yv || !mass || !radius) return fail(NBODY_GPU_EINVAL, "NULL argument");
+    if (cfg->n < 1) return fail(NBODY_GPU_EINVAL, "n must be >= 1 (got %d)", cfg->n);
+    if (cfg->xdim < 1 || cfg->ydim < 1) return fail(NBODY_GPU_EINVAL, "xdim/ydim must be >= 1");
+    if (cfg->mode != NBODY_GPU_MODE_EXACT && cfg->mode != NBODY_GPU_MODE_FAST)
+        return fail(NBODY_GPU_EINVAL, "unknown mode %d", cfg->mode);
+    nbody_gpu *h = new (std::nothrow) nbody_gpu();
+    if (!h) return fail(NBODY_GPU_ENOMEM, "out of host memory");
+    int rc = init_impl(h, cfg, x, y, xv, yv, mass, radius);
+    if (rc) {
+        char keep[sizeof g_err];
+        memcpy(keep, g_err, sizeof keep);
+        nbody_gpu_destroy(h);
+        memcpy(g_err, keep, sizeof keep);
+        return rc;
+    }
+    *out = h;
+    return NBODY_GPU_OK;
+}
+
+int nbody_gpu_set_state(nbody_gpu *h, const double *x, const double *y, const double *xv, const double *yv)
+{
+    if (!h || !x || !y || !xv || !yv) return fail(NBODY_GPU_EINVAL, "NULL argument");
+    int rc = sync_all(h);
+    if (!rc) rc = upload(h, nullptr, h->cur, x, y);
+    if (!rc) rc = upload(h, &Shard::vel, 0, xv, yv);
+    if (rc) return rc;
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        NB_CUDA(cudaMemsetAsync(s.frc, 0, sizeof(double2) * static_cast<size_t>(h->npad), s.stream));
+    }
+    return NBODY_GPU_OK;
+}
+
+int nbody_gpu_step(nbody_gpu *h, int steps)
+{
+    if (!h) return fail(NBODY_GPU_EINVAL, "handle is NULL");
+    return do_steps(h, steps);
+}
+
+int nbody_gpu_step_timed(nbody_gpu *h, int steps, float *ms)
+{
+    if (!h || !ms) return fail(NBODY_GPU_EINVAL, "NULL argument");
+    int rc = sync_all(h);
+    if (rc) return rc;
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        NB_CUDA(cudaEventRecord(s.ev0, s.stream));
+    }
+    rc = do_steps(h, steps);
+    if (rc) return rc;
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        NB_CUDA(cudaEventRecord(s.ev1, s.stream));
+    }
+    float worst = 0.f;
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        NB_CUDA(cudaEventSynchronize(s.ev1));
+        float t = 0.f;
+        NB_CUDA(cudaEventElapsedTime(&t, s.ev0, s.ev1));
+        if (t > worst) worst = t;
+    }
+    *ms = worst;
+    return NBODY_GPU_OK;
+}
+
+int nbody_gpu_sync(nbody_gpu *h)
+{
+    if (!h) return fail(NBODY_GPU_EINVAL, "handle is NULL");
+    return sync_all(h);
+}
+
+static int download(nbody_gpu *h, const double2 *src, cudaStream_t st, double *a, double *b)
+{
+    if (!a && !b) return NBODY_GPU_OK;
+    NB_CUDA(cudaMemcpyAsync(h->stage, src, sizeof(double2) * static_cast<size_t>(h->n), cudaMemcpyDeviceToHost, st));
+    NB_CUDA(cudaStreamSynchronize(st));
+    for (int i = 0; i < h->n; ++i) {
+        if (a) a[i] = h->stage[i].x;
+        if (b) b[i] = h->stage[i].y;
+    }
+    return NBODY_GPU_OK;
+}
+
+int nbody_gpu_forces(nbody_gpu *h, double *xf, double *yf)
+{
+    if (!h) return fail(NBODY_GPU_EINVAL, "handle is NULL");
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        if (h->cfg.mode == NBODY_GPU_MODE_FAST) {
+            launch_forces_fast(force_args(h, s, h->cur), h->nsplit, s.stream);
+            launch_reduce_fast(integrate_args(h, s, h->cur), s.stream);
+            h->launches[2] += 1;
+        } else {
+            launch_forces_exact(force_args(h, s, h->cur), s.stream);
+        }
+        h->launches[0] += 1;
+        NB_CUDA(cudaGetLastError());
+    }
+    int rc = allgather(h, 3);
+    if (rc) return rc;
+    Shard &s0 = h->shards[0];
+    NB_CUDA(cudaSetDevice(s0.device));
+    rc = download(h, s0.frc, s0.stream, xf, yf);
+    if (rc) return rc;
+    return sync_all(h);
+}
+
+int nbody_gpu_fetch(nbody_gpu *h, double *x, double *y, double *xf, double *yf, double *xv, double *yv)
+{
+    if (!h) return fail(NBODY_GPU_EINVAL, "handle is NULL");
+    int rc = NBODY_GPU_OK;
+    if (h->sharded) {
+        // forces and velocities live sharded during the run; gather them like the reference's
+        // whole-struct MPI_Allgatherv leaves them (nbody-par.c:933-936)
+        if (xv || yv) rc = allgather(h, 2);
+        if (!rc && (xf || yf)) rc = allgather(h, 3);
+        if (rc) return rc;
+    }
+    Shard &s0 = h->shards[0];
+    NB_CUDA(cudaSetDevice(s0.device));
+    rc = download(h, s0.pos[h->cur], s0.stream, x, y);
+    if (!rc) rc = download(h, s0.frc, s0.stream, xf, yf);
+    if (!rc) rc = download(h, s0.vel, s0.stream, xv, yv);
+    if (rc) return rc;
+    rc = sync_all(h);
+    if (rc) return rc;
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        NB_CUDA(cudaGetLastError());
+    }
+    return NBODY_GPU_OK;
+}
+
+long long nbody_gpu_launch_count(const nbody_gpu *h, long long out[4])
+{
+    if (!h) return 0;
+    long long t = 0;
+    for (int k = 0; k < 4; ++k) {
+        if (out) out[k] = h->launches[k];
+        t += h->launches[k];
+    }
+    return t;
+}
+
+}  // extern "C"

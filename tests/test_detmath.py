@@ -1,0 +1,97 @@
+"""Accuracy and special-case checks of include/nbody_detmath.h (host build, via the oracle library).
+The GPU side of the same header is checked bit-for-bit by tests/test_gpu_parity.py."""
+import math
+
+import numpy as np
+import pytest
+
+
+def ulps(got, want):
+    return np.abs(got - want) / np.spacing(np.abs(want))
+
+
+def sample_xy(n, seed):
+    rng = np.random.default_rng(seed)
+    y = rng.uniform(-1024, 1024, n)
+    x = rng.uniform(-1024, 1024, n)
+    q = n // 4
+    x[:q] *= rng.uniform(0, 1, q) ** 8
+    y[q:2 * q] *= rng.uniform(0, 1, q) ** 8
+    y[-1000:] = 0.0
+    x[-500:] = -np.abs(x[-500:])
+    return y, x
+
+
+def test_atan2_within_2ulp_of_libm(oracle):
+    L = oracle.lib()
+    n = 400000
+    y, x = sample_xy(n, 7)
+    a, b = np.empty(n), np.empty(n)
+    L.oracle_det_atan2_v(n, y, x, a)
+    L.oracle_libm_atan2_v(n, y, x, b)
+    assert ulps(a, b).max() <= 2.0
+    assert (a == b).mean() > 0.9
+
+
+def test_sincos_within_1ulp_of_libm_on_atan2_range(oracle):
+    L = oracle.lib()
+    n = 400000
+    y, x = sample_xy(n, 11)
+    ang = np.empty(n)
+    L.oracle_libm_atan2_v(n, y, x, ang)
+    s1, c1, s2, c2 = (np.empty(n) for _ in range(4))
+    L.oracle_det_sincos_v(n, ang, s1, c1)
+    L.oracle_libm_sincos_v(n, ang, s2, c2)
+    assert ulps(s1, s2).max() <= 1.0
+    assert ulps(c1, c2).max() <= 1.0
+
+
+def test_against_mpmath(oracle):
+    mp = pytest.importorskip("mpmath")
+    mp.mp.prec = 120
+    L = oracle.lib()
+    n = 3000
+    y, x = sample_xy(n, 3)
+    a = np.empty(n)
+    L.oracle_det_atan2_v(n, y, x, a)
+    worst = 0.0
+    for k in range(n):
+        t = mp.atan2(mp.mpf(y[k]), mp.mpf(x[k]))
+        if t != 0:
+            worst = max(worst, float(abs(mp.mpf(a[k]) - t) / mp.mpf(np.spacing(abs(float(t))))))
+    assert worst <= 1.6, worst
+    s, c = np.empty(n), np.empty(n)
+    L.oracle_det_sincos_v(n, a, s, c)
+    ws = wc = 0.0
+    for k in range(n):
+        ts, tc = mp.sin(mp.mpf(a[k])), mp.cos(mp.mpf(a[k]))
+        ws = max(ws, float(abs(mp.mpf(s[k]) - ts) / mp.mpf(np.spacing(abs(float(ts))))) if ts != 0 else 0.0)
+        wc = max(wc, float(abs(mp.mpf(c[k]) - tc) / mp.mpf(np.spacing(abs(float(tc))))) if tc != 0 else 0.0)
+    assert ws <= 1.1 and wc <= 1.1, (ws, wc)
+
+
+def test_atan2_special_cases_follow_c99(oracle):
+    L = oracle.lib()
+    cases = [(0.0, 0.0), (0.0, -0.0), (-0.0, -0.0), (-0.0, 0.0), (0.0, -3.0), (-0.0, -3.0), (2.0, 0.0), (-2.0, 0.0),
+             (2.0, -0.0), (1.0, 1.0), (1.0, -1.0), (-1.0, -1.0), (-1.0, 1.0), (0.0, 5.0), (1e-300, 1e-300),
+             (1e-310, 1.0), (3.0, 1e-320), (5e-324, 5e-324), (1e300, 1e-300), (1e-300, -1e300)]
+    y = np.array([c[0] for c in cases])
+    x = np.array([c[1] for c in cases])
+    out = np.empty(len(cases))
+    L.oracle_det_atan2_v(len(cases), y, x, out)
+    for (yy, xx), got in zip(cases, out):
+        want = math.atan2(yy, xx)
+        assert math.copysign(1, got) == math.copysign(1, want), (yy, xx, got, want)
+        assert abs(got - want) <= 2 * np.spacing(abs(want)), (yy, xx, got, want)
+
+
+def test_sincos_key_values(oracle):
+    L = oracle.lib()
+    a = np.array([0.0, math.pi, -math.pi, math.pi / 2, -math.pi / 2, math.pi / 4, 3.0, -3.0, 1e-300, 100.0, -1e4])
+    s, c = np.empty(a.size), np.empty(a.size)
+    L.oracle_det_sincos_v(a.size, a, s, c)
+    for k in range(a.size):
+        assert abs(s[k] - math.sin(a[k])) <= 1.5 * np.spacing(abs(math.sin(a[k]))), a[k]
+        assert abs(c[k] - math.cos(a[k])) <= 1.5 * np.spacing(abs(math.cos(a[k]))), a[k]
+    assert s[0] == 0.0 and c[0] == 1.0
+    assert s[1] == math.sin(math.pi)      # 1.2246e-16: the reference's yf for dy=0, dx<0 is not zero
