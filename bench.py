@@ -1,0 +1,337 @@
+#!/usr/bin/env python
+"""bench.py -- FP64 pair-interactions/s of the all-pairs N-body step on B200.
+
+    python bench.py --gpus N --steps K --warmup W            (N > 1: launched under torchrun)
+    python bench.py --impl reference --gpus N --steps K --warmup W
+
+Workload (BASELINE.json config 4, the one `metric` is quoted on): N = 262144 bodies from the
+reference initialiser (srand(27102015), world 1024x768; reference nbody/nbody-par.c:208-222),
+fast mode, STRONG scaling: the same 262144 bodies are row-sharded over the GPUs and the new
+positions are all-gathered every step (ncclAllGather replaces MPI_Allgatherv, nbody-par.c:913).
+A step = one force + integrate (+ exchange) pass.  value = K * N * (N-1) / t, t = device time of
+the K-step loop (CUDA events on the library's stream), max over ranks.
+
+e2e: the same metric through the C ABI with HOST buffers every step: nbody_gpu_set_state (H2D
+from the library's pinned staging) -> nbody_gpu_step(1) -> nbody_gpu_fetch (D2H), wall clock.
+
+roofline: the force kernel is FP64-pipe bound (neither HBM nor tensor): achieved = algorithmic
+flops by the reference's own model (nbody-seq.c:367-380: 20 flop per unordered pair = 10 per
+directed pair-interaction) / the kernel's mean duration from per-launch CUDA events inside the
+timed region; peak = the DFMA rate measured live by nbody_gpu_fp64_peak (MEASURED_PEAKS.json has
+no FP64 figure).  pipe_frac = FP64-pipe instructions actually issued per pair (SASS count,
+confirmed by ncu sm__inst_executed_pipe_fp64) x pairs/s / (peak/2): the utilisation figure the
+north star's "% of FP64 pipe peak" means (IEEE-grade rsqrt makes one pair ~19 pipe instructions,
+so the algorithmic-flop fraction cannot approach 1).
+
+--impl reference: the reference's CPU algorithm (oracle port, libm trig, row form = nbody-par's
+pass B, nbody-par.c:302-308) on all host cores, each step a bounded sample of rows of the same
+N = 262144 workload.  The oracle is only ever executed in that arm and in cpu_baseline.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "fp64_pair_interactions_per_s"
+UNIT = "pair-interactions/s"
+N_DEFAULT = 262144
+XDIM, YDIM = 1024, 768
+FP64_INSTR_PER_PAIR = {"fast": 19}   # SASS count of the fast inner loop (profiles/), FP64-pipe ops only
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=N_DEFAULT)
+    ap.add_argument("--mode", default="fast", choices=["fast", "exact"])
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index):
+        self.idx = device_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [t.strip() for t in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------------------------
+def cpu_sample(oracle_lib, b, n, threads, budget_s):
+    """Bounded CPU sample of the same workload: rows [0,R) x all N columns, oracle row form with
+    libm trig on `threads` host threads.  Returns (pairs/s, description)."""
+    L = oracle_lib.lib()
+    xf, yf = np.zeros(n), np.zeros(n)
+    rows = max(threads, 8)
+    t0 = time.perf_counter()
+    L.oracle_forces_rows(n, 0, 0, rows, threads, b.x, b.y, b.mass, b.radius, xf, yf)
+    dt = time.perf_counter() - t0
+    rate = rows * (n - 1.0) / dt
+    rows2 = int(max(rows, min(n, budget_s * rate / (n - 1.0))))
+    rows2 = max(threads, rows2 // threads * threads)
+    t0 = time.perf_counter()
+    L.oracle_forces_rows(n, 0, 0, rows2, threads, b.x, b.y, b.mass, b.radius, xf, yf)
+    dt = time.perf_counter() - t0
+    return rows2 * (n - 1.0) / dt, rows2, dt
+
+
+def cpu_seq_sample(oracle_lib, b, n, budget_s):
+    """nbody-seq's own form: triangular walk, one core; 2 directed interactions per evaluation."""
+    L = oracle_lib.lib()
+    xf, yf = np.zeros(n), np.zeros(n)
+    rows = 4
+    t0 = time.perf_counter()
+    ev = L.oracle_forces_symmetric_sample(n, 0, 0, rows, b.x, b.y, b.mass, b.radius, xf, yf)
+    dt = time.perf_counter() - t0
+    rows2 = max(rows, int(budget_s * (ev / dt) / n))
+    t0 = time.perf_counter()
+    ev = L.oracle_forces_symmetric_sample(n, 0, 0, rows2, b.x, b.y, b.mass, b.radius, xf, yf)
+    dt = time.perf_counter() - t0
+    return 2.0 * ev / dt, rows2, dt
+
+
+def run_reference(args, rank, world):
+    """The reference arm: CPU only, rank 0 only."""
+    if rank != 0:
+        return
+    import oracle_lib
+    n = args.n
+    threads = os.cpu_count() or 1
+    b = oracle_lib.init_bodies(n, XDIM, YDIM)
+    L = oracle_lib.lib()
+    xf, yf = np.zeros(n), np.zeros(n)
+    # size one "step" = a rows sample worth ~2 s so that steps+warmup stay within minutes
+    t0 = time.perf_counter()
+    L.oracle_forces_rows(n, 0, 0, 4 * threads, threads, b.x, b.y, b.mass, b.radius, xf, yf)
+    probe = time.perf_counter() - t0
+    rows = max(threads, int(2.0 / probe * 4 * threads) // threads * threads)
+    rows = min(rows, n)
+    xn, yn = np.zeros(n), np.zeros(n)
+
+    def one_step():
+        L.oracle_forces_rows(n, 0, 0, rows, threads, b.x, b.y, b.mass, b.radius, xf, yf)
+        L.oracle_velocities(rows, 0, xf, yf, b.mass, b.xv, b.yv)
+        L.oracle_positions(rows, XDIM, YDIM, b.x, b.y, b.xv, b.yv, xn, yn)
+
+    for _ in range(args.warmup):
+        one_step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        one_step()
+    dt = time.perf_counter() - t0
+    value = args.steps * rows * (n - 1.0) / dt
+    sample = "rows [0,%d) x all %d columns per step (%.3g of a full step), oracle row form, libm trig" % (
+        rows, n, rows / float(n))
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3 * (n / float(rows)),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": {"workload": "N=%d bodies, reference initialiser, world %dx%d; "
+                                            "CPU sample of rows" % (n, XDIM, YDIM), "n": n},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "ms_per_step is the sample time scaled to a full step (x N/rows)"}
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return 0
+
+    import torch
+    import pnb200
+    import oracle_lib   # body initialiser + cpu_baseline leg only; never on the measured GPU path
+    nb = pnb200.load()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    nccl_id = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        idt = torch.zeros(nb.NCCL_ID_BYTES, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(nb.nccl_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        nccl_id = bytes(idt.cpu().numpy().tobytes())
+
+    n = args.n
+    mode = nb.MODE_FAST if args.mode == "fast" else nb.MODE_EXACT
+    b = oracle_lib.init_bodies(n, XDIM, YDIM)      # the reference's initial state (synthetic)
+    g = nb.NBodyGPU(b.x, b.y, b.xv, b.yv, b.mass, b.radius, xdim=XDIM, ydim=YDIM, mode=mode,
+                    device=local_rank, rank=rank, nranks=world, nccl_id=nccl_id)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def maxreduce(v):
+        if dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    peak_tf, _ = nb.fp64_peak(local_rank, 200)
+
+    # ---- device-resident timed region ------------------------------------------------------
+    g.step(args.warmup)
+    g.sync()
+    l0 = sum(g.launch_count()[1][:3])   # our kernels only (force, integrate, reduce), not NCCL's
+    sampler = ClockSampler(local_rank)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    prof = g.step_profiled(args.steps, flush_l2=True)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    launches = sum(g.launch_count()[1][:3]) - l0
+    t_ms = maxreduce(prof["total"])
+    force_ms = maxreduce(prof["force"])
+    integ_ms = maxreduce(prof["integrate"])
+    exch_ms = maxreduce(prof["exchange"])
+    pairs_per_step = n * (n - 1.0)
+    value = args.steps * pairs_per_step / (t_ms * 1e-3)
+
+    # ---- end to end through the C ABI with host buffers every step --------------------------
+    e2e = None
+    if not args.no_e2e:
+        x, y, xf, yf, xv, yv = g.fetch()
+        e_steps = max(2, min(args.steps, 5))
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e_steps):
+            g.set_state(x, y, xv, yv)          # H2D: positions + velocities
+            g.step(1)
+            x, y, xf, yf, xv, yv = g.fetch()   # D2H: the six columns the reference prints
+        barrier()
+        e_dt = maxreduce(time.perf_counter() - t0)
+        e2e = {"value": e_steps * pairs_per_step / e_dt, "unit": UNIT,
+               "h2d_bytes_per_step": 4 * 8 * n, "d2h_bytes_per_step": 6 * 8 * n, "steps": e_steps,
+               "call": "nbody_gpu_set_state + nbody_gpu_step(1) + nbody_gpu_fetch per step, wall clock"}
+
+    if rank != 0:
+        g.close()
+        if dist is not None:
+            dist.destroy_process_group()
+        return 0
+
+    # ---- roofline of the dominant kernel (force kernel) -------------------------------------
+    rows = (n + world - 1) // world
+    launch_pairs = rows * (n - 1.0)                       # pair-interactions one force launch evaluates
+    launch_s = force_ms * 1e-3 / args.steps
+    algo_tflops = 10.0 * launch_pairs / launch_s / 1e12   # reference flop model: 10 per directed pair
+    ipp = FP64_INSTR_PER_PAIR.get(args.mode)
+    roofline = {"bound": "fp64", "achieved": algo_tflops, "peak": peak_tf, "unit": "TFLOP/s",
+                "frac": algo_tflops / peak_tf, "traffic": None,
+                "peak_source": "measured live: nbody_gpu_fp64_peak DFMA kernel on this GPU "
+                               "(MEASURED_PEAKS.json has no FP64 entry)",
+                "kernel": "forces_kernel<%s>" % args.mode, "kernel_ms_per_launch": launch_s * 1e3,
+                "kernel_share_of_step": force_ms / t_ms,
+                "algorithmic_flops_per_pair": 10, "pairs_per_launch": launch_pairs}
+    if ipp:
+        roofline["fp64_pipe_instr_per_pair"] = ipp
+        roofline["pipe_frac"] = ipp * (launch_pairs / launch_s) / (peak_tf * 1e12 / 2.0)
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        v, rws, dt = cpu_sample(oracle_lib, b, n, threads, args.cpu_seconds)
+        v1, rws1, dt1 = cpu_seq_sample(oracle_lib, b, n, min(6.0, args.cpu_seconds / 2))
+        cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": "rows [0,%d) x all %d columns of the same N=%d workload, oracle row form (nbody-par pass B), "
+                         "libm trig, %.1f s" % (rws, n, n, dt),
+               "seq_1core": {"value": v1, "cores": 1,
+                             "sample": "triangular walk rows [0,%d) (nbody-seq form, 2 interactions per evaluation), "
+                                       "%.1f s" % (rws1, dt1)}}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": t_ms / args.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "BASELINE config 4: N=%d bodies, reference initialiser (srand 27102015), world %dx%d, "
+                                   "%s mode, rows sharded over %d GPU(s), all-gather of new positions per step"
+                                   % (n, XDIM, YDIM, args.mode, world),
+                       "n": n, "mode": args.mode, "parallelism": "row-shard x%d" % world,
+                       "l2": "256 MiB scratch overwritten between steps (L2 flush); working set per step 8 MiB"},
+            "steps_per_s": args.steps / (t_ms * 1e-3),
+            "phase_ms_per_step": {"force": force_ms / args.steps, "integrate": integ_ms / args.steps,
+                                  "exchange": exch_ms / args.steps},
+            "clocks": clocks, "gpu_launches": launches, "roofline": roofline}
+    if e2e:
+        line["e2e"] = e2e
+    if cpu:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line), flush=True)
+    g.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

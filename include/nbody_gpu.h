@@ -87,6 +87,14 @@ int nbody_gpu_step(nbody_gpu *h, int steps);
  * synchronised; *ms receives the device time (max over this handle's devices). */
 int nbody_gpu_step_timed(nbody_gpu *h, int steps, float *ms);
 
+/* As nbody_gpu_step_timed with plain launches and a CUDA event between the phases of every
+ * step: out_ms[0] = whole span, [1] = sum of force-kernel spans, [2] = integrate kernels,
+ * [3] = position exchange (0 when not sharded); each the max over this handle's devices.
+ * flush_l2 != 0 overwrites a 256 MiB scratch buffer between steps (inside the whole span,
+ * outside the per-phase spans) so that no step starts with the previous step's L2 contents.
+ * This is the reference's --measure-comm (nbody-par.c:912,918) done with device timers. */
+int nbody_gpu_step_profiled(nbody_gpu *h, int steps, int flush_l2, float out_ms[4]);
+
 /* compute_forces only (clear_forces + compute_forces, nbody-seq.c:458-459) on the
  * current positions; state is otherwise untouched.  Synchronous. */
 int nbody_gpu_forces(nbody_gpu *h, double *xf, double *yf);

@@ -118,6 +118,29 @@ void oracle_forces_symmetric(int n, int trig, const double *x, const double *y,
     }
 }
 
+/* A bounded SAMPLE of the triangular walk for CPU-baseline timing: rows b in [lo,hi) only,
+ * each against every c > b (nbody-seq.c:87-107).  xf/yf receive partial sums (timing only).
+ * Returns the number of pair evaluations done; each is two directed pair-interactions. */
+long long oracle_forces_symmetric_sample(int n, int trig, int lo, int hi,
+                                         const double *x, const double *y,
+                                         const double *mass, const double *radius,
+                                         double *xf, double *yf)
+{
+    long long evals = 0;
+    for (int b = lo; b < hi; ++b) {
+        for (int c = b + 1; c < n; ++c) {
+            double fx, fy;
+            pair_force(trig, x[b], y[b], mass[b], radius[b], x[c], y[c], mass[c], radius[c], &fx, &fy);
+            xf[b] += fx;
+            yf[b] += fy;
+            xf[c] -= fx;
+            yf[c] -= fy;
+        }
+        evals += n - 1 - b;
+    }
+    return evals;
+}
+
 /* The same sums, one body at a time: body i receives -f(j,i) for j<i then +f(i,j)
  * for j>i, j ascending -- the order in which the triangular loop above touches
  * XF(i)/YF(i).  Bit-identical to oracle_forces_symmetric (tests check it), twice
@@ -129,7 +152,7 @@ void oracle_forces_rows(int n, int trig, int lo, int hi, int threads,
                         double *xf, double *yf)
 {
     if (threads < 1) threads = 1;
-#pragma omp parallel for schedule(dynamic, 16) num_threads(threads)
+#pragma omp parallel for schedule(dynamic, 1) num_threads(threads)
     for (int i = lo; i < hi; ++i) {
         double ax = 0, ay = 0;
         for (int j = 0; j < i; ++j) {

@@ -59,6 +59,7 @@ def lib():
     L.nbody_gpu_set_state.argtypes = [vp] + [_dp] * 4
     L.nbody_gpu_step.argtypes = [vp, ci]
     L.nbody_gpu_step_timed.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_float)]
+    L.nbody_gpu_step_profiled.argtypes = [vp, ci, ci, ctypes.POINTER(ctypes.c_float)]
     L.nbody_gpu_forces.argtypes = [vp, _dp, _dp]
     L.nbody_gpu_fetch.argtypes = [vp] + [odp] * 6
     L.nbody_gpu_sync.argtypes = [vp]
@@ -145,6 +146,12 @@ class NBodyGPU:
         ms = ctypes.c_float()
         _check(lib().nbody_gpu_step_timed(self._h, int(steps), ctypes.byref(ms)))
         return ms.value
+
+    def step_profiled(self, steps=1, flush_l2=False):
+        """Plain launches with events between phases: dict(total, force, integrate, exchange) in ms."""
+        out = (ctypes.c_float * 4)()
+        _check(lib().nbody_gpu_step_profiled(self._h, int(steps), int(bool(flush_l2)), out))
+        return dict(total=out[0], force=out[1], integrate=out[2], exchange=out[3])
 
     def forces(self):
         xf, yf = np.empty(self.n), np.empty(self.n)

@@ -1,5 +1,6 @@
 // kernels_fast.cu -- FAST-mode instantiations (FMA contraction on, algebraic force direction).
 #include "step_kernels.cuh"
+#include "forces_fast.cuh"
 
 namespace nbody {
 
@@ -7,8 +8,8 @@ void launch_forces_fast(const ForceArgs &a, int nsplit, cudaStream_t st)
 {
     const int rows = a.hi - a.lo;
     if (rows <= 0) return;
-    dim3 grid((rows + FORCE_THREADS - 1) / FORCE_THREADS, nsplit);
-    forces_kernel<MODE_FAST><<<grid, FORCE_THREADS, 0, st>>>(a);
+    dim3 grid((rows + FAST_ROWS_PER_CTA - 1) / FAST_ROWS_PER_CTA, nsplit);
+    forces_fast_kernel<<<grid, FORCE_THREADS, 0, st>>>(a);
 }
 
 void launch_integrate_fast(const IntegrateArgs &a, cudaStream_t st)

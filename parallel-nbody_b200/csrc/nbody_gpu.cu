@@ -488,6 +488,81 @@ int nbody_gpu_step_timed(nbody_gpu *h, int steps, float *ms)
     return NBODY_GPU_OK;
 }
 
+int nbody_gpu_step_profiled(nbody_gpu *h, int steps, int flush_l2, float out_ms[4])
+{
+    if (!h || !out_ms || steps < 0) return fail(NBODY_GPU_EINVAL, "bad argument");
+    int rc = sync_all(h);
+    if (rc) return rc;
+    const size_t flush_bytes = 256u << 20;
+    const size_t nsh = h->shards.size();
+    // events: per shard, per step: t0 (before force), t1 (after force), t2 (after integrate), t3 (after exchange)
+    std::vector<cudaEvent_t> ev(nsh * (static_cast<size_t>(steps) * 4 + 2), nullptr);
+    std::vector<void *> scratch(nsh, nullptr);
+    auto E = [&](size_t k, int step, int which) -> cudaEvent_t & {
+        return ev[k * (static_cast<size_t>(steps) * 4 + 2) + static_cast<size_t>(step) * 4 + which];
+    };
+    for (size_t k = 0; k < nsh; ++k) {
+        NB_CUDA(cudaSetDevice(h->shards[k].device));
+        for (size_t e = 0; e < static_cast<size_t>(steps) * 4 + 2; ++e)
+            NB_CUDA(cudaEventCreate(&ev[k * (static_cast<size_t>(steps) * 4 + 2) + e]));
+        if (flush_l2) NB_CUDA(cudaMalloc(&scratch[k], flush_bytes));
+    }
+    const int last = steps * 4;   // index of the two span events: E(k, steps, 0) and E(k, steps, 1)
+    (void)last;
+    for (size_t k = 0; k < nsh; ++k) {
+        NB_CUDA(cudaSetDevice(h->shards[k].device));
+        NB_CUDA(cudaEventRecord(E(k, steps, 0), h->shards[k].stream));
+    }
+    for (int st = 0; st < steps; ++st) {
+        for (size_t k = 0; k < nsh; ++k) {
+            Shard &s = h->shards[k];
+            NB_CUDA(cudaSetDevice(s.device));
+            if (flush_l2) NB_CUDA(cudaMemsetAsync(scratch[k], st & 0xff, flush_bytes, s.stream));
+            NB_CUDA(cudaEventRecord(E(k, st, 0), s.stream));
+            if (h->cfg.mode == NBODY_GPU_MODE_FAST) launch_forces_fast(force_args(h, s, h->cur), h->nsplit, s.stream);
+            else launch_forces_exact(force_args(h, s, h->cur), s.stream);
+            NB_CUDA(cudaEventRecord(E(k, st, 1), s.stream));
+            if (h->cfg.mode == NBODY_GPU_MODE_FAST) launch_integrate_fast(integrate_args(h, s, h->cur), s.stream);
+            else launch_integrate_exact(integrate_args(h, s, h->cur), s.stream);
+            NB_CUDA(cudaEventRecord(E(k, st, 2), s.stream));
+        }
+        h->launches[0] += static_cast<long long>(nsh);
+        h->launches[1] += static_cast<long long>(nsh);
+        rc = allgather(h, h->cur ^ 1);
+        if (rc) return rc;
+        for (size_t k = 0; k < nsh; ++k) {
+            NB_CUDA(cudaSetDevice(h->shards[k].device));
+            NB_CUDA(cudaEventRecord(E(k, st, 3), h->shards[k].stream));
+        }
+        h->cur ^= 1;
+    }
+    for (size_t k = 0; k < nsh; ++k) {
+        NB_CUDA(cudaSetDevice(h->shards[k].device));
+        NB_CUDA(cudaEventRecord(E(k, steps, 1), h->shards[k].stream));
+    }
+    for (int q = 0; q < 4; ++q) out_ms[q] = 0.f;
+    for (size_t k = 0; k < nsh; ++k) {
+        NB_CUDA(cudaSetDevice(h->shards[k].device));
+        NB_CUDA(cudaEventSynchronize(E(k, steps, 1)));
+        float acc[4] = {0.f, 0.f, 0.f, 0.f}, t = 0.f;
+        NB_CUDA(cudaEventElapsedTime(&acc[0], E(k, steps, 0), E(k, steps, 1)));
+        for (int st = 0; st < steps; ++st) {
+            for (int q = 0; q < 3; ++q) {
+                NB_CUDA(cudaEventElapsedTime(&t, E(k, st, q), E(k, st, q + 1)));
+                acc[q + 1] += t;
+            }
+        }
+        if (!h->sharded) acc[3] = 0.f;
+        for (int q = 0; q < 4; ++q)
+            if (acc[q] > out_ms[q]) out_ms[q] = acc[q];
+        for (size_t e = 0; e < static_cast<size_t>(steps) * 4 + 2; ++e)
+            cudaEventDestroy(ev[k * (static_cast<size_t>(steps) * 4 + 2) + e]);
+        if (scratch[k]) cudaFree(scratch[k]);
+        NB_CUDA(cudaGetLastError());
+    }
+    return NBODY_GPU_OK;
+}
+
 int nbody_gpu_sync(nbody_gpu *h)
 {
     if (!h) return fail(NBODY_GPU_EINVAL, "handle is NULL");

@@ -31,6 +31,8 @@ def lib():
     L.oracle_init_bodies.argtypes = [i, i, i] + [_dp] * 6
     L.oracle_forces_symmetric.argtypes = [i, i] + [_dp] * 6
     L.oracle_forces_rows.argtypes = [i, i, i, i, i] + [_dp] * 6
+    L.oracle_forces_symmetric_sample.argtypes = [i, i, i, i] + [_dp] * 6
+    L.oracle_forces_symmetric_sample.restype = ctypes.c_longlong
     L.oracle_velocities.argtypes = [i, i] + [_dp] * 5
     L.oracle_positions.argtypes = [i, i, i] + [_dp] * 6
     L.oracle_run.argtypes = [i, i, i, i, i, i] + [_dp] * 8

@@ -1,0 +1,92 @@
+"""CPU-side checks of the C-ABI library: it loads, exports every symbol include/nbody_gpu.h declares,
+its pure host helpers match the reference's rules, and without a GPU it fails loudly (no fallback)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "nbody_gpu.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(nbody_gpu_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol(nb):
+    L = ctypes.CDLL(nb.LIB_PATH)
+    names = declared_symbols()
+    assert len(names) >= 15
+    for nm in names:
+        assert hasattr(L, nm), nm
+    assert L.nbody_gpu_abi_version() == 1
+
+
+def test_header_compiles_as_c(tmp_path):
+    src = tmp_path / "t.c"
+    src.write_text('#include "nbody_gpu.h"\nint main(void){ nbody_gpu_cfg c = {0}; return c.n; }\n')
+    import subprocess
+    subprocess.run(["/usr/bin/gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), "-c", str(src),
+                    "-o", str(tmp_path / "t.o")], check=True)
+
+
+def ref_partition(n, p):
+    """Python restatement of nbody-par.c:225-250."""
+    counts = [n // p] * p
+    r = n % p
+    while r > 0:
+        counts[r] += 1
+        r -= 1
+    displs = [0] * p
+    for k in range(1, p):
+        displs[k] = displs[k - 1] + counts[k - 1]
+    return counts, displs
+
+
+@pytest.mark.parametrize("n,p", [(128, 1), (128, 8), (10, 4), (32, 2), (10000, 6), (7, 8), (262144, 8), (1000, 7)])
+def test_partitions(nb, n, p):
+    assert nb.partition_reference(n, p) == ref_partition(n, p)
+    rows = -(-n // p)
+    covered = []
+    for r in range(p):
+        lo, hi = nb.partition(n, p, r)
+        assert lo == min(n, r * rows) and hi == min(n, (r + 1) * rows)
+        covered += list(range(lo, hi))
+    assert covered == list(range(n))   # every body owned exactly once, in order
+
+
+def test_argument_errors(nb):
+    z = np.zeros(4)
+    with pytest.raises(nb.NBodyGPUError, match="mode"):
+        nb.NBodyGPU(z, z, z, z, z + 1, z + 1, mode=7)
+    with pytest.raises(nb.NBodyGPUError, match="xdim"):
+        nb.NBodyGPU(z, z, z, z, z + 1, z + 1, xdim=0)
+    with pytest.raises(ValueError):
+        nb.NBodyGPU(z, z[:3], z, z, z, z)
+
+
+def test_no_silent_cpu_fallback(nb):
+    """Without a usable CUDA device the product path must raise, never compute on the CPU."""
+    if nb.device_count() > 0:
+        pytest.skip("a GPU is present")
+    z = np.ones(8)
+    with pytest.raises(nb.NBodyGPUError, match="CUDA|cuda|device"):
+        nb.NBodyGPU(z, z, z, z, z, z)
+    with pytest.raises(nb.NBodyGPUError):
+        nb.fp64_peak(0, 10)
+
+
+def test_product_sources_do_not_reference_the_oracle():
+    """oracle/ is test infrastructure: nothing under the package, include/ or nbody/ may name it."""
+    bad = []
+    for top in ("parallel-nbody_b200", "include", "nbody"):
+        for dp, _, files in os.walk(os.path.join(ROOT, top)):
+            for f in files:
+                if f.endswith((".cu", ".cuh", ".h", ".c", ".py", "Makefile")):
+                    txt = open(os.path.join(dp, f), errors="ignore").read()
+                    if re.search(r"#\s*include[^\n]*oracle|liboracle|oracle_[a-z_]+\s*\(|import\s+oracle|-loracle", txt):
+                        bad.append(os.path.join(dp, f))
+    assert not bad, bad
