@@ -45,7 +45,7 @@ METRIC = "fp64_pair_interactions_per_s"
 UNIT = "pair-interactions/s"
 N_DEFAULT = 262144
 XDIM, YDIM = 1024, 768
-FP64_INSTR_PER_PAIR = {"fast": 19}   # SASS count of the fast inner loop (profiles/), FP64-pipe ops only
+FP64_INSTR_PER_PAIR = {"fast": 16}   # SASS count of the fast inner loop (profiles/), FP64-pipe ops only
 
 
 def parse():

@@ -24,7 +24,7 @@
 
 namespace nbody {
 
-constexpr int FAST_IB = 2;                                  // bodies i per thread
+constexpr int FAST_IB = 2;                                  // bodies i per thread (default variant)
 constexpr int FAST_ROWS_PER_CTA = FORCE_THREADS * FAST_IB;  // 256
 
 __device__ __forceinline__ double rsqrt_seed(double q)
@@ -40,6 +40,7 @@ struct FastBody {
     int minhi;        // min over j of the high word of dsqr: 0 <=> some dsqr == 0
 };
 
+template <bool IMAX>
 __device__ __forceinline__ void pair_fast2(FastBody &b, double xj, double yj, double mj, double rj)
 {
     const double dx = xj - b.x;
@@ -47,7 +48,13 @@ __device__ __forceinline__ void pair_fast2(FastBody &b, double xj, double yj, do
     const double dsqr = fma(dx, dx, dy * dy);
     const double mindist = b.r + rj;
     const double mindsqr = mindist * mindist;
-    const double forced = fmax(dsqr, mindsqr);
+    double forced;
+    if (IMAX) {
+        // both operands are >= 0: IEEE order == integer order of the bit patterns (keeps the compare off the FP64 pipe)
+        forced = __longlong_as_double(max(__double_as_longlong(dsqr), __double_as_longlong(mindsqr)));
+    } else {
+        forced = fmax(dsqr, mindsqr);
+    }
     b.minhi = min(b.minhi, __double2hiint(dsqr));
     const double f2 = forced * forced;
     const double q = fma(f2, dsqr, 1e-290);
@@ -80,14 +87,15 @@ __device__ __noinline__ double coincident_rescan(const double2 *s_pos, const dou
     return ax;
 }
 
-__global__ void __launch_bounds__(FORCE_THREADS) forces_fast_kernel(const ForceArgs a)
+template <int IB, int UNROLL, int MINB, bool IMAX>
+__global__ void __launch_bounds__(FORCE_THREADS, MINB) forces_fast_kernel(const ForceArgs a)
 {
     __shared__ alignas(128) double2 s_pos[STAGES][TILE_J];
     __shared__ alignas(128) double2 s_mr[STAGES][TILE_J];
     __shared__ alignas(8) uint64_t s_full[STAGES];
 
     const int tid = threadIdx.x;
-    const int ibase = a.lo + blockIdx.x * FAST_ROWS_PER_CTA + tid;
+    const int ibase = a.lo + blockIdx.x * (FORCE_THREADS * IB) + tid;
     const int j0 = blockIdx.y * a.chunk;
     const int j1 = min(a.n, j0 + a.chunk);
     const int ntiles = (j1 - j0 + TILE_J - 1) / TILE_J;
@@ -110,11 +118,11 @@ __global__ void __launch_bounds__(FORCE_THREADS) forces_fast_kernel(const ForceA
         for (int t = 0; t < STAGES && t < ntiles; ++t) issue(t);
     }
 
-    FastBody b[FAST_IB];
-    int idx[FAST_IB];
-    double gm[FAST_IB];
+    FastBody b[IB];
+    int idx[IB];
+    double gm[IB];
 #pragma unroll
-    for (int k = 0; k < FAST_IB; ++k) {
+    for (int k = 0; k < IB; ++k) {
         idx[k] = ibase + k * FORCE_THREADS;
         const bool live = idx[k] < a.hi;
         const double2 p = live ? a.pos[idx[k]] : make_double2(0.0, 0.0);
@@ -130,15 +138,15 @@ __global__ void __launch_bounds__(FORCE_THREADS) forces_fast_kernel(const ForceA
         mbar_wait(&s_full[st], (tile / STAGES) & 1);
         const int jb = j0 + tile * TILE_J;
         const int cnt = min(TILE_J, j1 - jb);
-#pragma unroll 4
+#pragma unroll UNROLL
         for (int jj = 0; jj < cnt; ++jj) {
             const double2 pj = s_pos[st][jj];
             const double2 qj = s_mr[st][jj];
 #pragma unroll
-            for (int k = 0; k < FAST_IB; ++k) pair_fast2(b[k], pj.x, pj.y, qj.x, qj.y);
+            for (int k = 0; k < IB; ++k) pair_fast2<IMAX>(b[k], pj.x, pj.y, qj.x, qj.y);
         }
 #pragma unroll
-        for (int k = 0; k < FAST_IB; ++k) {
+        for (int k = 0; k < IB; ++k) {
             if (b[k].minhi == 0) {   // a coincident body (or body i itself) was in this tile
                 b[k].ax += coincident_rescan(&s_pos[st][0], &s_mr[st][0], cnt, jb, idx[k], b[k].x, b[k].y, b[k].r);
                 b[k].minhi = 0x7fffffff;
@@ -149,7 +157,7 @@ __global__ void __launch_bounds__(FORCE_THREADS) forces_fast_kernel(const ForceA
     }
 
 #pragma unroll
-    for (int k = 0; k < FAST_IB; ++k) {
+    for (int k = 0; k < IB; ++k) {
         if (idx[k] < a.hi)
             a.out[static_cast<size_t>(blockIdx.y) * a.npad + idx[k]] = make_double2(gm[k] * b[k].ax, gm[k] * b[k].ay);
     }

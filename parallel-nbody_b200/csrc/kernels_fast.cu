@@ -1,4 +1,6 @@
 // kernels_fast.cu -- FAST-mode instantiations (FMA contraction on, algebraic force direction).
+#include <cstdlib>
+
 #include "step_kernels.cuh"
 #include "forces_fast.cuh"
 
@@ -8,8 +10,26 @@ void launch_forces_fast(const ForceArgs &a, int nsplit, cudaStream_t st)
 {
     const int rows = a.hi - a.lo;
     if (rows <= 0) return;
-    dim3 grid((rows + FAST_ROWS_PER_CTA - 1) / FAST_ROWS_PER_CTA, nsplit);
-    forces_fast_kernel<<<grid, FORCE_THREADS, 0, st>>>(a);
+    // development knob: NBODY_FAST_VARIANT selects a tuning variant (default 0)
+    static const int variant = getenv("NBODY_FAST_VARIANT") ? atoi(getenv("NBODY_FAST_VARIANT")) : 0;
+#define NB_LAUNCH(IB, UN, MINB, IMAX)                                                            \
+    {                                                                                             \
+        dim3 grid((rows + FORCE_THREADS * IB - 1) / (FORCE_THREADS * IB), nsplit);                \
+        forces_fast_kernel<IB, UN, MINB, IMAX><<<grid, FORCE_THREADS, 0, st>>>(a);                \
+    }
+    switch (variant) {
+    default: NB_LAUNCH(2, 4, 1, true) break;
+    case 10: NB_LAUNCH(2, 4, 1, false) break;
+    case 1: NB_LAUNCH(2, 4, 8, false) break;
+    case 2: NB_LAUNCH(2, 2, 1, false) break;
+    case 3: NB_LAUNCH(4, 2, 1, false) break;
+    case 4: NB_LAUNCH(1, 8, 1, false) break;
+    case 6: NB_LAUNCH(2, 4, 8, true) break;
+    case 7: NB_LAUNCH(4, 2, 1, true) break;
+    case 8: NB_LAUNCH(2, 8, 1, false) break;
+    case 9: NB_LAUNCH(1, 4, 1, true) break;
+    }
+#undef NB_LAUNCH
 }
 
 void launch_integrate_fast(const IntegrateArgs &a, cudaStream_t st)
