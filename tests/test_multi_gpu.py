@@ -1,0 +1,53 @@
+"""Row sharding over several GPUs of one process (cfg.ngpus = K, ncclCommInitAll + ncclAllGather):
+results must be bit-identical to the single-GPU run in BOTH modes (each body's sum is formed whole on
+one GPU in the single-GPU order; fast-mode chunking depends on N only).  Skipped with < 2 GPUs; the
+one-process-per-GPU shape is exercised by bench.py under torchrun and by tests/test_multirank_cpu.py."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(nb, b, mode, ngpus, steps):
+    g = nb.NBodyGPU(b.x, b.y, b.xv, b.yv, b.mass, b.radius, mode=mode, ngpus=ngpus)
+    g.step(steps)
+    out = g.fetch()
+    g.close()
+    return out
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("n,steps", [(128, 50), (1001, 8), (4096, 3), (5, 20)])
+def test_sharded_equals_single_gpu_bits(nb, oracle, mode, n, steps):
+    k = nb.device_count()
+    if k < 2:
+        pytest.skip("needs >= 2 GPUs")
+    b = oracle.init_bodies(n)
+    ref = _run(nb, b, mode, 1, steps)
+    for p in sorted({2, min(k, 3), k}):
+        got = _run(nb, b, mode, p, steps)
+        for a, c in zip(ref, got):
+            assert np.array_equal(a.view(np.uint64), c.view(np.uint64)), (mode, n, p)
+
+
+def test_sharded_exact_matches_oracle_and_golden(nb, oracle):
+    k = nb.device_count()
+    if k < 2:
+        pytest.skip("needs >= 2 GPUs")
+    b = oracle.init_bodies(128)
+    got = _run(nb, b, 0, k, 1000)
+    assert oracle.format_state(*got) == oracle.golden_text("128_MY_REF_OUTPUT_128x1000.txt")
+    oracle.run(b, 1000, trig=1)
+    for a, f in zip(got, ("x", "y", "xf", "yf", "xv", "yv")):
+        assert np.array_equal(a.view(np.uint64), getattr(b, f).view(np.uint64)), f
+
+
+def test_forces_only_sharded(nb, oracle):
+    k = nb.device_count()
+    if k < 2:
+        pytest.skip("needs >= 2 GPUs")
+    b = oracle.init_bodies(3000)
+    g1 = nb.NBodyGPU(b.x, b.y, b.xv, b.yv, b.mass, b.radius, mode=1, ngpus=1)
+    g2 = nb.NBodyGPU(b.x, b.y, b.xv, b.yv, b.mass, b.radius, mode=1, ngpus=k)
+    a, c = g1.forces(), g2.forces()
+    assert np.array_equal(a[0], c[0]) and np.array_equal(a[1], c[1])
