@@ -63,7 +63,8 @@ typedef struct nbody_gpu_cfg {
     const void *nccl_id;
     int jsplit;     /* fast mode: number of fixed j-chunks (0 = library default for n) */
     int use_graph;  /* 1 = capture the step loop in a CUDA graph (default when 0: yes), -1 = plain launches */
-    int fused;      /* 1 = integrate inside the force kernel's epilogue where possible; 0 = default; -1 = never */
+    int symmetric;  /* fast mode: 1 = evaluate each unordered pair once (+f to i, -f to j, like nbody-seq.c:103-106),
+                       -1 = directed evaluation only, 0 = library default (symmetric on one GPU for n >= 8192) */
 } nbody_gpu_cfg;
 
 /* Replaces calloc(world) + initialize_simulation_data + MPI_Bcast

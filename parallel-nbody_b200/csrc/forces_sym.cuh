@@ -1,0 +1,266 @@
+// forces_sym.cuh -- FAST-mode force kernel that evaluates every unordered pair ONCE.
+//
+// The reference's compute_forces walks the upper triangle and gives +f to body b and -f
+// to body c (nbody-seq.c:87-107).  This kernel does the same on the GPU: bodies are cut
+// into row blocks of SYM_RB; CTA (block B, j-chunk s) keeps SYM_IB bodies i of block B
+// per thread in registers and walks the j tiles of chunk s
+//   * below the block: skipped (those pairs belong to the block that owns j),
+//   * inside the block (diagonal tiles): directed evaluation, both directions, no reaction,
+//   * above the block: one evaluation per pair; +f accumulates in registers for body i
+//     (row sum) and the reaction on body j is reduced over the 32 lanes by a shuffle
+//     butterfly, over the 8 warps through shared memory, and written ONCE per (block, j) to
+//     colpart[B][j] -- no atomics, fixed order, so the result is deterministic.
+// integrate_kernel / reduce_partials_kernel then form
+//     F(i) = sum_{B < block(i)} colpart[B][i]  +  sum_{s >= chunk(block(i))} rowpart[s][i]
+// in that fixed order.  Per unordered pair: 19 FP64-pipe instructions (13 shared, 3 per side)
+// + 1 MUFU + ~8 ALU/LSU + 0.3 SHFL, against 2 x (16 + ...) for the directed kernel.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+#include "forces_fast.cuh"
+
+namespace nbody {
+
+struct SymBody {
+    double x, y, r, m;   // position, radius, mass
+    double ax, ay;       // row accumulators (without the m_i*G factor)
+    int minhi;
+};
+
+// One unordered pair (i < j): row side into b.ax/ay, reaction side into (rx, ry).
+__device__ __forceinline__ void pair_sym(SymBody &b, double xj, double yj, double mj, double rj, double &rx,
+                                         double &ry)
+{
+    const double dx = xj - b.x;
+    const double dy = yj - b.y;
+    const double dsqr = fma(dx, dx, dy * dy);
+    const double mindist = b.r + rj;
+    const double mindsqr = mindist * mindist;
+    const double forced = __longlong_as_double(max(__double_as_longlong(dsqr), __double_as_longlong(mindsqr)));
+    b.minhi = min(b.minhi, __double2hiint(dsqr));
+    const double f2 = forced * forced;
+    const double q = fma(f2, dsqr, 1e-290);
+    const double y0 = rsqrt_seed(q);
+    const double t = q * y0;
+    const double e = fma(-t, y0, 1.0);
+    const double p = fma(e, 0.375, 0.5);
+    const double ye = y0 * e;
+    const double y1 = fma(ye, p, y0);        // 1 / (forced * sqrt(dsqr))
+    const double zi = mj * y1;
+    b.ax = fma(zi, dx, b.ax);
+    b.ay = fma(zi, dy, b.ay);
+    const double zj = b.m * y1;
+    rx = fma(zj, dx, rx);
+    ry = fma(zj, dy, ry);
+}
+
+// Directed evaluation (diagonal tiles), same arithmetic as forces_fast.cuh.
+__device__ __forceinline__ void pair_dir(SymBody &b, double xj, double yj, double mj, double rj)
+{
+    const double dx = xj - b.x;
+    const double dy = yj - b.y;
+    const double dsqr = fma(dx, dx, dy * dy);
+    const double mindist = b.r + rj;
+    const double mindsqr = mindist * mindist;
+    const double forced = __longlong_as_double(max(__double_as_longlong(dsqr), __double_as_longlong(mindsqr)));
+    b.minhi = min(b.minhi, __double2hiint(dsqr));
+    const double f2 = forced * forced;
+    const double q = fma(f2, dsqr, 1e-290);
+    const double y0 = rsqrt_seed(q);
+    const double t = q * y0;
+    const double e = fma(-t, y0, 1.0);
+    const double p = fma(e, 0.375, 0.5);
+    const double z0 = mj * y0;
+    const double ze = z0 * e;
+    const double s = fma(ze, p, z0);
+    b.ax = fma(s, dx, b.ax);
+    b.ay = fma(s, dy, b.ay);
+}
+
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    return v;
+}
+
+constexpr int SYM_THREADS = 256;
+constexpr int SYM_WARPS = SYM_THREADS / 32;
+constexpr int SYM_IB = 2;
+constexpr int SYM_SMEM_BYTES = STAGES * TILE_J * 16 * 2 + SYM_WARPS * TILE_J * 16 + 64;
+static_assert(SYM_RB == SYM_THREADS * SYM_IB, "row block = threads x bodies per thread");
+static_assert(SYM_RB % TILE_J == 0, "row blocks must be tile aligned");
+
+// Rare path, row side of a tile above the block (all j > i): + m_j / mindsqr for coincident j.
+__device__ __noinline__ double sym_row_rescan(const double2 *s_pos, const double2 *s_mr, int cnt, double xi, double yi,
+                                              double ri)
+{
+    double ax = 0.0;
+    for (int jj = 0; jj < cnt; ++jj) {
+        const double2 pj = s_pos[jj];
+        if (pj.x == xi && pj.y == yi) {
+            const double2 qj = s_mr[jj];
+            const double md = ri + qj.y;
+            ax += qj.x / (md * md);
+        }
+    }
+    return ax;
+}
+
+// Rare path, column side: sum over the block's bodies i (all < j) coincident with body j of m_i / mindsqr.
+__device__ __noinline__ double sym_col_rescan(const double2 *pos, const double2 *mr, int i0, int i1, double xj,
+                                              double yj, double rj)
+{
+    double c = 0.0;
+    for (int i = i0; i < i1; ++i) {
+        const double2 pi = pos[i];
+        if (pi.x == xj && pi.y == yj) {
+            const double2 qi = mr[i];
+            const double md = qi.y + rj;
+            c += qi.x / (md * md);
+        }
+    }
+    return c;
+}
+
+__global__ void __launch_bounds__(SYM_THREADS) forces_sym_kernel(const SymArgs a)
+{
+    extern __shared__ __align__(128) unsigned char sym_smem[];
+    double2 *s_pos = reinterpret_cast<double2 *>(sym_smem);                 // [STAGES][TILE_J]
+    double2 *s_mr = s_pos + STAGES * TILE_J;                                // [STAGES][TILE_J]
+    double2 *s_col = s_mr + STAGES * TILE_J;                                // [SYM_WARPS][TILE_J]
+    uint64_t *s_full = reinterpret_cast<uint64_t *>(s_col + SYM_WARPS * TILE_J);
+    int *s_flag = reinterpret_cast<int *>(s_full + STAGES);                 // [2]
+
+    const int tid = threadIdx.x;
+    const int lane = tid & 31;
+    const int warp = tid >> 5;
+    const int blk = a.block_first + blockIdx.x * a.block_stride;           // row block index
+    const int i0 = blk * SYM_RB;
+    const int i1 = min(a.n, i0 + SYM_RB);
+    const int jc0 = blockIdx.y * a.chunk;
+    const int j1 = min(a.n, jc0 + a.chunk);
+    const int j0 = max(jc0, i0);            // tiles below the block are not ours (tile aligned: chunk % SYM_RB == 0)
+    if (j0 >= j1) return;                   // whole chunk below the block: nothing is read from this (B, s)
+    const int ntiles = (j1 - j0 + TILE_J - 1) / TILE_J;
+
+    if (tid == 0) {
+        for (int s = 0; s < STAGES; ++s) mbar_init(&s_full[s], 1);
+        mbar_init_fence();
+        s_flag[0] = 0;
+        s_flag[1] = 0;
+    }
+    __syncthreads();
+
+    auto issue = [&](int tile) {
+        const int st = tile % STAGES;
+        const int jb = j0 + tile * TILE_J;
+        const uint32_t bytes = static_cast<uint32_t>(min(TILE_J, j1 - jb)) * sizeof(double2);
+        mbar_arrive_expect_tx(&s_full[st], 2 * bytes);
+        tma_load_1d(s_pos + st * TILE_J, a.pos + jb, bytes, &s_full[st]);
+        tma_load_1d(s_mr + st * TILE_J, a.mr + jb, bytes, &s_full[st]);
+    };
+    if (tid == 0) {
+        for (int t = 0; t < STAGES && t < ntiles; ++t) issue(t);
+    }
+
+    SymBody b[SYM_IB];
+    int idx[SYM_IB];
+#pragma unroll
+    for (int k = 0; k < SYM_IB; ++k) {
+        idx[k] = i0 + tid + k * SYM_THREADS;
+        const bool live = idx[k] < a.n;
+        const double2 p = live ? a.pos[idx[k]] : make_double2(0.0, 0.0);
+        const double2 q = live ? a.mr[idx[k]] : make_double2(0.0, 1.0);   // mass 0: no reaction from padding rows
+        b[k].x = p.x; b[k].y = p.y; b[k].m = q.x; b[k].r = q.y;
+        b[k].ax = 0.0; b[k].ay = 0.0;
+        b[k].minhi = 0x7fffffff;
+    }
+
+    for (int tile = 0; tile < ntiles; ++tile) {
+        const int st = tile % STAGES;
+        mbar_wait(&s_full[st], (tile / STAGES) & 1);
+        const int jb = j0 + tile * TILE_J;
+        const int cnt = min(TILE_J, j1 - jb);
+        const double2 *tp = s_pos + st * TILE_J;
+        const double2 *tm = s_mr + st * TILE_J;
+        const bool diag = jb < i0 + SYM_RB;   // block-uniform
+
+        if (diag) {
+#pragma unroll 4
+            for (int jj = 0; jj < cnt; ++jj) {
+                const double2 pj = tp[jj];
+                const double2 qj = tm[jj];
+#pragma unroll
+                for (int k = 0; k < SYM_IB; ++k) pair_dir(b[k], pj.x, pj.y, qj.x, qj.y);
+            }
+#pragma unroll
+            for (int k = 0; k < SYM_IB; ++k) {
+                if (b[k].minhi == 0) {
+                    b[k].ax += coincident_rescan(tp, tm, cnt, jb, idx[k], b[k].x, b[k].y, b[k].r);
+                    b[k].minhi = 0x7fffffff;
+                }
+            }
+            __syncthreads();
+        } else {
+            for (int g = 0; g < cnt; g += 32) {
+                double cx = 0.0, cy = 0.0;
+                const int gn = min(32, cnt - g);
+#pragma unroll 4
+                for (int u = 0; u < gn; ++u) {
+                    const double2 pj = tp[g + u];
+                    const double2 qj = tm[g + u];
+                    double rx = 0.0, ry = 0.0;
+#pragma unroll
+                    for (int k = 0; k < SYM_IB; ++k) pair_sym(b[k], pj.x, pj.y, qj.x, qj.y, rx, ry);
+                    rx = warp_sum(rx);
+                    ry = warp_sum(ry);
+                    if (lane == u) { cx = rx; cy = ry; }
+                }
+                s_col[warp * TILE_J + g + lane] = make_double2(cx, cy);   // lanes >= gn write zeros
+            }
+            bool hit = false;
+#pragma unroll
+            for (int k = 0; k < SYM_IB; ++k) {
+                if (b[k].minhi == 0) {
+                    if (idx[k] < a.n) {
+                        b[k].ax += sym_row_rescan(tp, tm, cnt, b[k].x, b[k].y, b[k].r);
+                        hit = true;
+                    }
+                    b[k].minhi = 0x7fffffff;
+                }
+            }
+            if (hit) s_flag[tile & 1] = 1;
+            __syncthreads();
+            // column side: one thread per j, warps summed in fixed order
+            if (tid < cnt) {
+                double cx = 0.0, cy = 0.0;
+#pragma unroll
+                for (int w = 0; w < SYM_WARPS; ++w) {
+                    const double2 c = s_col[w * TILE_J + tid];
+                    cx += c.x;
+                    cy += c.y;
+                }
+                const double2 pj = tp[tid];
+                const double2 qj = tm[tid];
+                if (s_flag[tile & 1]) cx += sym_col_rescan(a.pos, a.mr, i0, i1, pj.x, pj.y, qj.y);
+                const double gmj = -NB_GRAVITY * qj.x;
+                a.colpart[static_cast<size_t>(blk) * a.npad + jb + tid] = make_double2(gmj * cx, gmj * cy);
+            }
+            if (tid == 0) s_flag[(tile + 1) & 1] = 0;
+            __syncthreads();
+        }
+        if (tid == 0 && tile + STAGES < ntiles) issue(tile + STAGES);
+    }
+
+#pragma unroll
+    for (int k = 0; k < SYM_IB; ++k) {
+        if (idx[k] < a.n) {
+            const double gm = NB_GRAVITY * b[k].m;
+            a.rowpart[static_cast<size_t>(blockIdx.y) * a.npad + idx[k]] = make_double2(gm * b[k].ax, gm * b[k].ay);
+        }
+    }
+}
+
+}  // namespace nbody

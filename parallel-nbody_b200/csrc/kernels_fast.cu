@@ -3,6 +3,7 @@
 
 #include "step_kernels.cuh"
 #include "forces_fast.cuh"
+#include "forces_sym.cuh"
 
 namespace nbody {
 
@@ -37,6 +38,16 @@ void launch_integrate_fast(const IntegrateArgs &a, cudaStream_t st)
     const int rows = a.hi - a.lo;
     if (rows <= 0) return;
     integrate_kernel<MODE_FAST><<<(rows + 127) / 128, 128, 0, st>>>(a);
+}
+
+int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream_t st)
+{
+    if (nblocks_here <= 0) return 0;
+    cudaError_t e = cudaFuncSetAttribute(forces_sym_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SYM_SMEM_BYTES);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    dim3 grid(nblocks_here, nsplit);
+    forces_sym_kernel<<<grid, SYM_THREADS, SYM_SMEM_BYTES, st>>>(a);
+    return 0;
 }
 
 void launch_reduce_fast(const IntegrateArgs &a, cudaStream_t st)

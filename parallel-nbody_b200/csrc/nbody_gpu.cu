@@ -58,6 +58,7 @@ struct Shard {
     double2 *vel = nullptr;
     double2 *frc = nullptr;
     double2 *part = nullptr;
+    double2 *colpart = nullptr;  // symmetric fast kernel: reaction partial sums [nblocks][npad]
     NcclComm comm = nullptr;
     cudaGraphExec_t graph[2] = {nullptr, nullptr};   // indexed by the starting slot
 };
@@ -74,6 +75,8 @@ struct nbody_gpu {
     int npad = 0;                // P * rows_per_shard (leading dimension of every array)
     int nsplit = 1;              // fast mode: j-chunks
     int chunk = 0;               // fast mode: j-chunk length
+    bool symmetric = false;      // fast mode: evaluate each unordered pair once (forces_sym_kernel)
+    int nblocks = 0;             // symmetric: number of SYM_RB row blocks
     int cur = 0;                 // slot holding the current positions (the reference's world->old)
     int graph_steps = 0;         // steps captured per graph launch (even), 0 = graphs off
     bool sharded = false;
@@ -115,6 +118,18 @@ static void choose_split(int n, int requested, int *nsplit, int *chunk)
     *nsplit = (n + c - 1) / c;
 }
 
+// Symmetric kernel: chunks are multiples of SYM_RB; many small chunks keep the triangular work balanced.
+static void choose_split_sym(int n, int requested, int *nsplit, int *chunk)
+{
+    int c;
+    if (requested > 0) c = (n + requested - 1) / requested;
+    else c = n / 64;
+    if (c < 2048) c = 2048;
+    c = (c + SYM_RB - 1) / SYM_RB * SYM_RB;
+    *chunk = c;
+    *nsplit = (n + c - 1) / c;
+}
+
 static void free_shard(Shard &s)
 {
     cudaSetDevice(s.device);
@@ -126,6 +141,7 @@ static void free_shard(Shard &s)
     if (s.vel) cudaFree(s.vel);
     if (s.frc) cudaFree(s.frc);
     if (s.part) cudaFree(s.part);
+    if (s.colpart) cudaFree(s.colpart);
     if (s.ev0) cudaEventDestroy(s.ev0);
     if (s.ev1) cudaEventDestroy(s.ev1);
     if (s.comm) {
@@ -159,6 +175,8 @@ static IntegrateArgs integrate_args(const nbody_gpu *h, const Shard &s, int slot
     a.vel = s.vel;
     a.frc = s.frc;
     a.part = s.part;
+    a.colpart = h->symmetric ? s.colpart : nullptr;
+    a.chunk = h->chunk;
     a.nsplit = h->nsplit;
     a.npad = h->npad;
     a.lo = s.lo;
@@ -168,16 +186,39 @@ static IntegrateArgs integrate_args(const nbody_gpu *h, const Shard &s, int slot
     return a;
 }
 
+// Enqueue the force kernel of shard s on the positions in slot `slot`.
+static void enqueue_forces(nbody_gpu *h, Shard &s, int slot)
+{
+    if (h->cfg.mode != NBODY_GPU_MODE_FAST) {
+        launch_forces_exact(force_args(h, s, slot), s.stream);
+    } else if (h->symmetric) {
+        SymArgs a;
+        a.pos = s.pos[slot];
+        a.mr = s.mr;
+        a.rowpart = s.part;
+        a.colpart = s.colpart;
+        a.n = h->n;
+        a.npad = h->npad;
+        a.chunk = h->chunk;
+        a.block_first = 0;
+        a.block_stride = 1;
+        launch_forces_sym(a, h->nblocks, h->nsplit, s.stream);
+    } else {
+        launch_forces_fast(force_args(h, s, slot), h->nsplit, s.stream);
+    }
+}
+
+static void enqueue_integrate(nbody_gpu *h, Shard &s, int slot)
+{
+    if (h->cfg.mode == NBODY_GPU_MODE_FAST) launch_integrate_fast(integrate_args(h, s, slot), s.stream);
+    else launch_integrate_exact(integrate_args(h, s, slot), s.stream);
+}
+
 // Enqueue the two kernels of one step on shard s, reading slot `slot`.
 static void enqueue_step_kernels(nbody_gpu *h, Shard &s, int slot)
 {
-    if (h->cfg.mode == NBODY_GPU_MODE_FAST) {
-        launch_forces_fast(force_args(h, s, slot), h->nsplit, s.stream);
-        launch_integrate_fast(integrate_args(h, s, slot), s.stream);
-    } else {
-        launch_forces_exact(force_args(h, s, slot), s.stream);
-        launch_integrate_exact(integrate_args(h, s, slot), s.stream);
-    }
+    enqueue_forces(h, s, slot);
+    enqueue_integrate(h, s, slot);
 }
 
 }  // namespace nbody
@@ -354,7 +395,11 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
     h->sharded = P > 1;
     h->rows_per_shard = (h->n + P - 1) / P;
     h->npad = h->rows_per_shard * P;
-    if (cfg->mode == NBODY_GPU_MODE_FAST) choose_split(h->n, cfg->jsplit, &h->nsplit, &h->chunk);
+    h->symmetric = cfg->mode == NBODY_GPU_MODE_FAST && !h->sharded &&
+                   (cfg->symmetric > 0 || (cfg->symmetric == 0 && h->n >= 8192));
+    h->nblocks = (h->n + SYM_RB - 1) / SYM_RB;
+    if (h->symmetric) choose_split_sym(h->n, cfg->jsplit, &h->nsplit, &h->chunk);
+    else if (cfg->mode == NBODY_GPU_MODE_FAST) choose_split(h->n, cfg->jsplit, &h->nsplit, &h->chunk);
     else { h->nsplit = 1; h->chunk = h->n; }
     if (cfg->use_graph >= 0 && !h->sharded) {
         // small worlds are launch-bound: put more steps behind one graph launch
@@ -386,6 +431,10 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
         if (cfg->mode == NBODY_GPU_MODE_FAST) {
             NB_CUDA(cudaMalloc(&s.part, bytes * h->nsplit));
             NB_CUDA(cudaMemsetAsync(s.part, 0, bytes * h->nsplit, s.stream));
+            if (h->symmetric) {
+                NB_CUDA(cudaMalloc(&s.colpart, bytes * h->nblocks));
+                NB_CUDA(cudaMemsetAsync(s.colpart, 0, bytes * h->nblocks, s.stream));
+            }
         }
     }
     NB_CUDA(cudaMallocHost(&h->stage, sizeof(double2) * static_cast<size_t>(h->npad)));
@@ -519,11 +568,9 @@ int nbody_gpu_step_profiled(nbody_gpu *h, int steps, int flush_l2, float out_ms[
             NB_CUDA(cudaSetDevice(s.device));
             if (flush_l2) NB_CUDA(cudaMemsetAsync(scratch[k], st & 0xff, flush_bytes, s.stream));
             NB_CUDA(cudaEventRecord(E(k, st, 0), s.stream));
-            if (h->cfg.mode == NBODY_GPU_MODE_FAST) launch_forces_fast(force_args(h, s, h->cur), h->nsplit, s.stream);
-            else launch_forces_exact(force_args(h, s, h->cur), s.stream);
+            enqueue_forces(h, s, h->cur);
             NB_CUDA(cudaEventRecord(E(k, st, 1), s.stream));
-            if (h->cfg.mode == NBODY_GPU_MODE_FAST) launch_integrate_fast(integrate_args(h, s, h->cur), s.stream);
-            else launch_integrate_exact(integrate_args(h, s, h->cur), s.stream);
+            enqueue_integrate(h, s, h->cur);
             NB_CUDA(cudaEventRecord(E(k, st, 2), s.stream));
         }
         h->launches[0] += static_cast<long long>(nsh);
@@ -586,12 +633,10 @@ int nbody_gpu_forces(nbody_gpu *h, double *xf, double *yf)
     if (!h) return fail(NBODY_GPU_EINVAL, "handle is NULL");
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
+        enqueue_forces(h, s, h->cur);
         if (h->cfg.mode == NBODY_GPU_MODE_FAST) {
-            launch_forces_fast(force_args(h, s, h->cur), h->nsplit, s.stream);
             launch_reduce_fast(integrate_args(h, s, h->cur), s.stream);
             h->launches[2] += 1;
-        } else {
-            launch_forces_exact(force_args(h, s, h->cur), s.stream);
         }
         h->launches[0] += 1;
         NB_CUDA(cudaGetLastError());

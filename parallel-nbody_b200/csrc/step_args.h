@@ -22,13 +22,29 @@ struct ForceArgs {
     int chunk;            // FAST: j-chunk length; chunk s covers [s*chunk, min(n,(s+1)*chunk))
 };
 
+constexpr int SYM_RB = 512;         // rows per block of the symmetric (evaluate-each-pair-once) kernel
+
+struct SymArgs {
+    const double2 *pos;
+    const double2 *mr;
+    double2 *rowpart;     // [nsplit][npad]  row-side partial sums
+    double2 *colpart;     // [nblocks][npad] reaction (column-side) partial sums, valid for j >= (B+1)*SYM_RB
+    int n;
+    int npad;
+    int chunk;            // j-chunk length, a multiple of SYM_RB
+    int block_first;      // this launch handles row blocks block_first + k*block_stride, k = 0..grid.x-1
+    int block_stride;
+};
+
 struct IntegrateArgs {
     const double2 *pos_old;
     double2 *pos_new;
     const double2 *mr;
     double2 *vel;
     double2 *frc;          // FAST: written (sum of partials); EXACT: read
-    const double2 *part;   // FAST: partial sums
+    const double2 *part;   // FAST: partial sums (row side)
+    const double2 *colpart;  // FAST symmetric: reaction partial sums, else nullptr
+    int chunk;             // FAST symmetric: j-chunk length
     int nsplit;            // FAST: number of j-chunks
     int npad;
     int lo, hi;
@@ -41,5 +57,6 @@ void launch_integrate_exact(const IntegrateArgs &a, cudaStream_t st);
 void launch_forces_fast(const ForceArgs &a, int nsplit, cudaStream_t st);
 void launch_integrate_fast(const IntegrateArgs &a, cudaStream_t st);
 void launch_reduce_fast(const IntegrateArgs &a, cudaStream_t st);
+int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream_t st);   // returns cudaError_t
 
 }  // namespace nbody

@@ -243,6 +243,30 @@ __device__ __forceinline__ void integrate_body(const IntegrateArgs &a, int i, do
     a.pos_new[i] = make_double2(xn, yn);
 }
 
+// FAST: total force on body i from the partial sums, in a fixed order: reactions from lower row
+// blocks (block index ascending) first, then the row-side j-chunks (ascending) -- lower j first,
+// like the reference's loop.  Directed kernel: colpart == nullptr, all chunks are row-side.
+__device__ __forceinline__ void sum_partials(const IntegrateArgs &a, int i, double &xf, double &yf)
+{
+    xf = 0.0;
+    yf = 0.0;
+    int s0 = 0;
+    if (a.colpart) {
+        const int blk = i / SYM_RB;
+        for (int b = 0; b < blk; ++b) {
+            const double2 t = a.colpart[static_cast<size_t>(b) * a.npad + i];
+            xf += t.x;
+            yf += t.y;
+        }
+        s0 = (blk * SYM_RB) / a.chunk;
+    }
+    for (int s = s0; s < a.nsplit; ++s) {
+        const double2 t = a.part[static_cast<size_t>(s) * a.npad + i];
+        xf += t.x;
+        yf += t.y;
+    }
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(128) integrate_kernel(const IntegrateArgs a)
 {
@@ -256,13 +280,7 @@ __global__ void __launch_bounds__(128) integrate_kernel(const IntegrateArgs a)
     double xf, yf;
     if (MODE == MODE_FAST) {
         // fixed-order sum of the j-chunk partials: deterministic, independent of the GPU count
-        xf = 0.0;
-        yf = 0.0;
-        for (int s = 0; s < a.nsplit; ++s) {
-            const double2 t = a.part[static_cast<size_t>(s) * a.npad + i];
-            xf += t.x;
-            yf += t.y;
-        }
+        sum_partials(a, i, xf, yf);
         a.frc[i] = make_double2(xf, yf);
     } else {
         const double2 t = a.frc[i];
@@ -279,12 +297,8 @@ __global__ void __launch_bounds__(128) reduce_partials_kernel(const IntegrateArg
 {
     const int i = a.lo + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= a.hi) return;
-    double xf = 0.0, yf = 0.0;
-    for (int s = 0; s < a.nsplit; ++s) {
-        const double2 t = a.part[static_cast<size_t>(s) * a.npad + i];
-        xf += t.x;
-        yf += t.y;
-    }
+    double xf, yf;
+    sum_partials(a, i, xf, yf);
     a.frc[i] = make_double2(xf, yf);
 }
 

@@ -98,10 +98,12 @@ def test_exact_4096_config2_prefix_and_graph_independence(nb, oracle):
         assert np.array_equal(a.view(np.uint64), c.view(np.uint64))
 
 
+@pytest.mark.parametrize("symmetric", [-1, 1])
 @pytest.mark.parametrize("n,steps", [(2, 50), (128, 1000), (777, 20), (2048, 4), (4096, 6)])
-def test_fast_within_tolerance_of_reference_math(nb, oracle, n, steps):
+def test_fast_within_tolerance_of_reference_math(nb, oracle, n, steps, symmetric):
+    """symmetric = -1: directed kernel; 1: each unordered pair evaluated once (+f to i, -f to j)."""
     b = oracle.init_bodies(n)
-    g = make(nb, b, mode=nb.MODE_FAST)
+    g = make(nb, b, mode=nb.MODE_FAST, symmetric=symmetric)
     g.step(steps)
     got = g.fetch()
     oracle.run(b, steps, trig=0, threads=8)
@@ -112,10 +114,11 @@ def test_fast_jsplit_variants_agree(nb, oracle):
     b = oracle.init_bodies(3000)
     ref = b.copy()
     oracle.run(ref, 3, trig=0, threads=8)
-    for js in (1, 2, 3, 7, 11):
-        g = make(nb, b, mode=nb.MODE_FAST, jsplit=js)
-        g.step(3)
-        assert_fast_close(g.fetch(), ref, "jsplit=%d" % js)
+    for sym in (-1, 1):
+        for js in (1, 2, 3, 7, 11):
+            g = make(nb, b, mode=nb.MODE_FAST, jsplit=js, symmetric=sym)
+            g.step(3)
+            assert_fast_close(g.fetch(), ref, "jsplit=%d sym=%d" % (js, sym))
 
 
 def _kat_bodies(oracle):
@@ -144,7 +147,25 @@ def test_forces_only_known_cases(nb, oracle):
     assert np.array_equal(gy.view(np.uint64), yf.view(np.uint64))
     # coincident triple 0,1,2: lower index is pushed +x by each higher coincident body
     L.oracle_forces_symmetric(b.n, 0, b.x, b.y, b.mass, b.radius, xf, yf)
-    fx, fy = make(nb, b, mode=nb.MODE_FAST).forces()
+    scale = max(np.abs(xf).max(), np.abs(yf).max())
+    for sym in (-1, 1):
+        fx, fy = make(nb, b, mode=nb.MODE_FAST, symmetric=sym).forces()
+        assert np.abs(fx - xf).max() <= 1e-12 * scale, sym
+        assert np.abs(fy - yf).max() <= 1e-12 * scale, sym
+
+
+@pytest.mark.parametrize("symmetric", [-1, 1])
+def test_fast_coincident_bodies_across_blocks(nb, oracle, symmetric):
+    """Exactly coincident bodies far apart in index (different row blocks and tiles of the symmetric
+    kernel), including a triple, and a coincident pair inside one block: the reference's
+    atan2(0,0) = 0 convention gives the lower index (+force, 0), the higher (-force, 0)."""
+    n = 3000
+    b = oracle.init_bodies(n)
+    for i, j in ((3, 2900), (3, 1500), (700, 701), (511, 512), (1023, 2047), (0, n - 1)):
+        b.x[j], b.y[j] = b.x[i], b.y[i]
+    xf, yf = np.zeros(n), np.zeros(n)
+    oracle.lib().oracle_forces_symmetric(n, 0, b.x, b.y, b.mass, b.radius, xf, yf)
+    fx, fy = make(nb, b, mode=nb.MODE_FAST, symmetric=symmetric).forces()
     scale = max(np.abs(xf).max(), np.abs(yf).max())
     assert np.abs(fx - xf).max() <= 1e-12 * scale
     assert np.abs(fy - yf).max() <= 1e-12 * scale
@@ -193,8 +214,12 @@ def test_large_n_properties_fast(nb, oracle):
     and a sampled-row comparison against the oracle's row form."""
     n = 65536
     b = oracle.init_bodies(n)
-    g = make(nb, b, mode=nb.MODE_FAST)
+    g = make(nb, b, mode=nb.MODE_FAST)          # default at this size: the symmetric kernel
+    gd = make(nb, b, mode=nb.MODE_FAST, symmetric=-1)
+    fxd, fyd = gd.forces()
     fx, fy = g.forces()
+    fs = max(np.abs(fxd).max(), np.abs(fyd).max())
+    assert np.abs(fx - fxd).max() <= 1e-11 * fs and np.abs(fy - fyd).max() <= 1e-11 * fs
     fx2, fy2 = g.forces()
     assert np.array_equal(fx, fx2) and np.array_equal(fy, fy2)
     scale = np.abs(fx).sum()
