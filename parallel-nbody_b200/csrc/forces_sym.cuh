@@ -86,8 +86,35 @@ __device__ __forceinline__ double warp_sum(double v)
 }
 
 constexpr int SYM_THREADS = 256;
+constexpr int SYM_IB_ = 2;
+
+template <bool GUARD>
+__device__ __forceinline__ void sym_group(SymBody (&b)[SYM_IB_], const double2 *tp, const double2 *tm, int g, int cnt,
+                                          int lane, double2 *col)
+{
+    double cx = 0.0, cy = 0.0;
+    const int src = (lane + 1) & 31;
+#pragma unroll 4
+    for (int r = 0; r < 32; ++r) {
+        const int jj = g + ((lane + r) & 31);
+        double2 pj, qj;
+        if (GUARD && jj >= cnt) {
+            pj = make_double2(-1.0e6, -1.0e6);   // beyond the last body: massless, far away, never stored
+            qj = make_double2(0.0, 1.0);
+        } else {
+            pj = tp[jj];
+            qj = tm[jj];
+        }
+#pragma unroll
+        for (int k = 0; k < SYM_IB_; ++k) pair_sym(b[k], pj.x, pj.y, qj.x, qj.y, cx, cy);
+        cx = __shfl_sync(0xffffffffu, cx, src);
+        cy = __shfl_sync(0xffffffffu, cy, src);
+    }
+    col[g + lane] = make_double2(cx, cy);   // entries >= cnt are never read
+}
+
 constexpr int SYM_WARPS = SYM_THREADS / 32;
-constexpr int SYM_IB = 2;
+constexpr int SYM_IB = SYM_IB_;
 constexpr int SYM_SMEM_BYTES = STAGES * TILE_J * 16 * 2 + SYM_WARPS * TILE_J * 16 + 64;
 static_assert(SYM_RB == SYM_THREADS * SYM_IB, "row block = threads x bodies per thread");
 static_assert(SYM_RB % TILE_J == 0, "row blocks must be tile aligned");
@@ -204,21 +231,14 @@ __global__ void __launch_bounds__(SYM_THREADS) forces_sym_kernel(const SymArgs a
             }
             __syncthreads();
         } else {
-            for (int g = 0; g < cnt; g += 32) {
-                double cx = 0.0, cy = 0.0;
-                const int gn = min(32, cnt - g);
-#pragma unroll 4
-                for (int u = 0; u < gn; ++u) {
-                    const double2 pj = tp[g + u];
-                    const double2 qj = tm[g + u];
-                    double rx = 0.0, ry = 0.0;
-#pragma unroll
-                    for (int k = 0; k < SYM_IB; ++k) pair_sym(b[k], pj.x, pj.y, qj.x, qj.y, rx, ry);
-                    rx = warp_sum(rx);
-                    ry = warp_sum(ry);
-                    if (lane == u) { cx = rx; cy = ry; }
-                }
-                s_col[warp * TILE_J + g + lane] = make_double2(cx, cy);   // lanes >= gn write zeros
+            // 32 j's at a time.  Lane l starts on j = g + l and moves to the next j every step; the reaction
+            // accumulator of a j travels the other way (one lane down per step), so it meets every lane
+            // exactly once and after 32 steps lane l holds the warp's complete reaction sum for j = g + l:
+            // no reduction tree, no atomics, fixed order.
+            if (cnt == TILE_J) {
+                for (int g = 0; g < TILE_J; g += 32) sym_group<false>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J);
+            } else {
+                for (int g = 0; g < cnt; g += 32) sym_group<true>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J);
             }
             bool hit = false;
 #pragma unroll
