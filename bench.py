@@ -37,6 +37,11 @@ import time
 
 import numpy as np
 
+# stdout carries exactly one JSON line: NCCL's banner (NCCL_DEBUG=VERSION prints to stdout and ignores
+# NCCL_DEBUG_FILE) is raised to WARN, which prints the same banner to the debug file
+if os.environ.get("NCCL_DEBUG", "").upper().startswith("V"):
+    os.environ["NCCL_DEBUG"] = "WARN"
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -45,7 +50,6 @@ METRIC = "fp64_pair_interactions_per_s"
 UNIT = "pair-interactions/s"
 N_DEFAULT = 262144
 XDIM, YDIM = 1024, 768
-FP64_INSTR_PER_PAIR = {"fast": 16}   # SASS count of the fast inner loop (profiles/), FP64-pipe ops only
 
 
 def parse():
@@ -286,12 +290,14 @@ def main():
     launch_pairs = rows * (n - 1.0)                       # pair-interactions one force launch evaluates
     launch_s = force_ms * 1e-3 / args.steps
     algo_tflops = 10.0 * launch_pairs / launch_s / 1e12   # reference flop model: 10 per directed pair
-    ipp = FP64_INSTR_PER_PAIR.get(args.mode)
+    desc = g.describe()
+    ipp = desc.get("fp64_instr_per_pair") or None
     roofline = {"bound": "fp64", "achieved": algo_tflops, "peak": peak_tf, "unit": "TFLOP/s",
                 "frac": algo_tflops / peak_tf, "traffic": None,
                 "peak_source": "measured live: nbody_gpu_fp64_peak DFMA kernel on this GPU "
                                "(MEASURED_PEAKS.json has no FP64 entry)",
-                "kernel": "forces_kernel<%s>" % args.mode, "kernel_ms_per_launch": launch_s * 1e3,
+                "kernel": desc["kernel"], "evaluation": "symmetric (each unordered pair once)" if desc["symmetric"]
+                else "directed", "kernel_ms_per_launch": launch_s * 1e3,
                 "kernel_share_of_step": force_ms / t_ms,
                 "algorithmic_flops_per_pair": 10, "pairs_per_launch": launch_pairs}
     if ipp:

@@ -118,6 +118,11 @@ const char *nbody_gpu_last_error(void);
  * separately in out[0..3] if out != NULL); returns the total. */
 long long nbody_gpu_launch_count(const nbody_gpu *h, long long out[4]);
 
+/* One-line JSON description of how this handle runs the step (kernel, symmetric or directed
+ * evaluation, j-chunks, FP64-pipe instructions issued per directed pair-interaction): written to
+ * buf (at most len bytes, NUL-terminated); returns the length needed. For logs and bench.py. */
+int nbody_gpu_describe(const nbody_gpu *h, char *buf, int len);
+
 /* Row partition used for sharding: rank r owns rows [lo, hi).  Equal ceil(n/P) blocks
  * (the last ones may be short or empty) so that one ncclAllGather replaces
  * MPI_Allgatherv (nbody-par.c:913-917). */

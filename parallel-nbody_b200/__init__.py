@@ -66,6 +66,7 @@ def lib():
     L.nbody_gpu_destroy.argtypes = [vp]
     L.nbody_gpu_destroy.restype = None
     L.nbody_gpu_last_error.restype = ctypes.c_char_p
+    L.nbody_gpu_describe.argtypes = [vp, ctypes.c_char_p, ci]
     L.nbody_gpu_launch_count.argtypes = [vp, ctypes.POINTER(ctypes.c_longlong)]
     L.nbody_gpu_launch_count.restype = ctypes.c_longlong
     L.nbody_gpu_partition.argtypes = [ci, ci, ci, ctypes.POINTER(ci), ctypes.POINTER(ci)]
@@ -166,6 +167,12 @@ class NBodyGPU:
 
     def sync(self):
         _check(lib().nbody_gpu_sync(self._h))
+
+    def describe(self):
+        import json
+        buf = ctypes.create_string_buffer(512)
+        lib().nbody_gpu_describe(self._h, buf, 512)
+        return json.loads(buf.value.decode())
 
     def launch_count(self):
         out = (ctypes.c_longlong * 4)()

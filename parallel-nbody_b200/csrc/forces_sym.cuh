@@ -10,9 +10,8 @@
 //     (row sum) and the reaction on body j is reduced over the 32 lanes by a shuffle
 //     butterfly, over the 8 warps through shared memory, and written ONCE per (block, j) to
 //     colpart[B][j] -- no atomics, fixed order, so the result is deterministic.
-// integrate_kernel / reduce_partials_kernel then form
-//     F(i) = sum_{B < block(i)} colpart[B][i]  +  sum_{s >= chunk(block(i))} rowpart[s][i]
-// in that fixed order.  Per unordered pair: 19 FP64-pipe instructions (13 shared, 3 per side)
+// sym_reduce_kernel then folds the partial sums into SYM_V per-virtual-rank vectors (step_args.h) and
+// integrate_kernel adds those in a fixed order: the same bits on 1, 2, 4 or 8 GPUs.  Per unordered pair: 19 FP64-pipe instructions (13 shared, 3 per side)
 // + 1 MUFU + ~8 ALU/LSU + 0.3 SHFL, against 2 x (16 + ...) for the directed kernel.
 #pragma once
 #include <cuda_runtime.h>
@@ -85,11 +84,8 @@ __device__ __forceinline__ double warp_sum(double v)
     return v;
 }
 
-constexpr int SYM_THREADS = 256;
-constexpr int SYM_IB_ = 2;
-
-template <bool GUARD>
-__device__ __forceinline__ void sym_group(SymBody (&b)[SYM_IB_], const double2 *tp, const double2 *tm, int g, int cnt,
+template <int IB, bool GUARD>
+__device__ __forceinline__ void sym_group(SymBody (&b)[IB], const double2 *tp, const double2 *tm, int g, int cnt,
                                           int lane, double2 *col)
 {
     double cx = 0.0, cy = 0.0;
@@ -106,17 +102,14 @@ __device__ __forceinline__ void sym_group(SymBody (&b)[SYM_IB_], const double2 *
             qj = tm[jj];
         }
 #pragma unroll
-        for (int k = 0; k < SYM_IB_; ++k) pair_sym(b[k], pj.x, pj.y, qj.x, qj.y, cx, cy);
+        for (int k = 0; k < IB; ++k) pair_sym(b[k], pj.x, pj.y, qj.x, qj.y, cx, cy);
         cx = __shfl_sync(0xffffffffu, cx, src);
         cy = __shfl_sync(0xffffffffu, cy, src);
     }
     col[g + lane] = make_double2(cx, cy);   // entries >= cnt are never read
 }
 
-constexpr int SYM_WARPS = SYM_THREADS / 32;
-constexpr int SYM_IB = SYM_IB_;
-constexpr int SYM_SMEM_BYTES = STAGES * TILE_J * 16 * 2 + SYM_WARPS * TILE_J * 16 + 64;
-static_assert(SYM_RB == SYM_THREADS * SYM_IB, "row block = threads x bodies per thread");
+constexpr int sym_smem_bytes(int threads) { return STAGES * TILE_J * 16 * 2 + (threads / 32) * TILE_J * 16 + 64; }
 static_assert(SYM_RB % TILE_J == 0, "row blocks must be tile aligned");
 
 // Rare path, row side of a tile above the block (all j > i): + m_j / mindsqr for coincident j.
@@ -151,8 +144,11 @@ __device__ __noinline__ double sym_col_rescan(const double2 *pos, const double2 
     return c;
 }
 
+template <int SYM_THREADS, int SYM_IB>
 __global__ void __launch_bounds__(SYM_THREADS) forces_sym_kernel(const SymArgs a)
 {
+    static_assert(SYM_RB == SYM_THREADS * SYM_IB, "row block = threads x bodies per thread");
+    constexpr int SYM_WARPS = SYM_THREADS / 32;
     extern __shared__ __align__(128) unsigned char sym_smem[];
     double2 *s_pos = reinterpret_cast<double2 *>(sym_smem);                 // [STAGES][TILE_J]
     double2 *s_mr = s_pos + STAGES * TILE_J;                                // [STAGES][TILE_J]
@@ -163,13 +159,13 @@ __global__ void __launch_bounds__(SYM_THREADS) forces_sym_kernel(const SymArgs a
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int warp = tid >> 5;
-    const int blk = a.block_first + blockIdx.x * a.block_stride;           // row block index
+    const int blk = sym_owned_block(blockIdx.x, a.v0, a.nv);               // row block index
     const int i0 = blk * SYM_RB;
     const int i1 = min(a.n, i0 + SYM_RB);
     const int jc0 = blockIdx.y * a.chunk;
     const int j1 = min(a.n, jc0 + a.chunk);
     const int j0 = max(jc0, i0);            // tiles below the block are not ours (tile aligned: chunk % SYM_RB == 0)
-    if (j0 >= j1) return;                   // whole chunk below the block: nothing is read from this (B, s)
+    if (i0 >= a.n || j0 >= j1) return;      // block beyond the last body, or whole chunk below the block
     const int ntiles = (j1 - j0 + TILE_J - 1) / TILE_J;
 
     if (tid == 0) {
@@ -236,9 +232,9 @@ __global__ void __launch_bounds__(SYM_THREADS) forces_sym_kernel(const SymArgs a
             // exactly once and after 32 steps lane l holds the warp's complete reaction sum for j = g + l:
             // no reduction tree, no atomics, fixed order.
             if (cnt == TILE_J) {
-                for (int g = 0; g < TILE_J; g += 32) sym_group<false>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J);
+                for (int g = 0; g < TILE_J; g += 32) sym_group<SYM_IB, false>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J);
             } else {
-                for (int g = 0; g < cnt; g += 32) sym_group<true>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J);
+                for (int g = 0; g < cnt; g += 32) sym_group<SYM_IB, true>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J);
             }
             bool hit = false;
 #pragma unroll
@@ -254,19 +250,19 @@ __global__ void __launch_bounds__(SYM_THREADS) forces_sym_kernel(const SymArgs a
             if (hit) s_flag[tile & 1] = 1;
             __syncthreads();
             // column side: one thread per j, warps summed in fixed order
-            if (tid < cnt) {
+            for (int jt = tid; jt < cnt; jt += SYM_THREADS) {
                 double cx = 0.0, cy = 0.0;
 #pragma unroll
                 for (int w = 0; w < SYM_WARPS; ++w) {
-                    const double2 c = s_col[w * TILE_J + tid];
+                    const double2 c = s_col[w * TILE_J + jt];
                     cx += c.x;
                     cy += c.y;
                 }
-                const double2 pj = tp[tid];
-                const double2 qj = tm[tid];
+                const double2 pj = tp[jt];
+                const double2 qj = tm[jt];
                 if (s_flag[tile & 1]) cx += sym_col_rescan(a.pos, a.mr, i0, i1, pj.x, pj.y, qj.y);
                 const double gmj = -NB_GRAVITY * qj.x;
-                a.colpart[static_cast<size_t>(blk) * a.npad + jb + tid] = make_double2(gmj * cx, gmj * cy);
+                a.colpart[static_cast<size_t>(sym_local_block(blk, a.v0, a.nv)) * a.npad + jb + jt] = make_double2(gmj * cx, gmj * cy);
             }
             if (tid == 0) s_flag[(tile + 1) & 1] = 0;
             __syncthreads();
@@ -281,6 +277,35 @@ __global__ void __launch_bounds__(SYM_THREADS) forces_sym_kernel(const SymArgs a
             a.rowpart[static_cast<size_t>(blockIdx.y) * a.npad + idx[k]] = make_double2(gm * b[k].ax, gm * b[k].ay);
         }
     }
+}
+
+// vbuf[v][j] for the virtual ranks this device owns, one thread per (j, v).
+__global__ void __launch_bounds__(128) sym_reduce_kernel(const SymReduceArgs a)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= a.n) return;
+    const int v = a.v0 + blockIdx.y;
+    const int blk = j / SYM_RB;
+    double xf = 0.0, yf = 0.0;
+    for (int g0 = 0; g0 < blk; g0 += 2 * SYM_V) {   // v's blocks below block(j), B ascending: 16g+v, 16g+15-v
+        const int Bs[2] = {g0 + v, g0 + 2 * SYM_V - 1 - v};
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            if (Bs[q] < blk) {
+                const double2 t = a.colpart[static_cast<size_t>(sym_local_block(Bs[q], a.v0, a.nv)) * a.npad + j];
+                xf += t.x;
+                yf += t.y;
+            }
+        }
+    }
+    if (sym_vrank(blk) == v) {                // j's own row sums, chunk ascending
+        for (int s = (blk * SYM_RB) / a.chunk; s < a.nsplit; ++s) {
+            const double2 t = a.rowpart[static_cast<size_t>(s) * a.npad + j];
+            xf += t.x;
+            yf += t.y;
+        }
+    }
+    a.vbuf[static_cast<size_t>(v) * a.npad + j] = make_double2(xf, yf);
 }
 
 }  // namespace nbody

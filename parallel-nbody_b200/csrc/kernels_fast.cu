@@ -43,11 +43,23 @@ void launch_integrate_fast(const IntegrateArgs &a, cudaStream_t st)
 int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream_t st)
 {
     if (nblocks_here <= 0) return 0;
-    cudaError_t e = cudaFuncSetAttribute(forces_sym_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SYM_SMEM_BYTES);
-    if (e != cudaSuccess) return static_cast<int>(e);
+    static const int variant = getenv("NBODY_SYM_VARIANT") ? atoi(getenv("NBODY_SYM_VARIANT")) : 0;
     dim3 grid(nblocks_here, nsplit);
-    forces_sym_kernel<<<grid, SYM_THREADS, SYM_SMEM_BYTES, st>>>(a);
+    cudaError_t e;
+#define NB_SYM_LAUNCH(T, IB)                                                                                       \
+    e = cudaFuncSetAttribute(forces_sym_kernel<T, IB>, cudaFuncAttributeMaxDynamicSharedMemorySize, sym_smem_bytes(T)); \
+    if (e != cudaSuccess) return static_cast<int>(e);                                                              \
+    forces_sym_kernel<T, IB><<<grid, T, sym_smem_bytes(T), st>>>(a);
+    if (variant == 1) { NB_SYM_LAUNCH(256, 2) } else { NB_SYM_LAUNCH(128, 4) }
+#undef NB_SYM_LAUNCH
     return 0;
+}
+
+void launch_sym_reduce(const SymReduceArgs &a, cudaStream_t st)
+{
+    if (a.n <= 0 || a.nv <= 0) return;
+    dim3 grid((a.n + 127) / 128, a.nv);
+    sym_reduce_kernel<<<grid, 128, 0, st>>>(a);
 }
 
 void launch_reduce_fast(const IntegrateArgs &a, cudaStream_t st)

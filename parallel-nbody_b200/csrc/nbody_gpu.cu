@@ -58,7 +58,10 @@ struct Shard {
     double2 *vel = nullptr;
     double2 *frc = nullptr;
     double2 *part = nullptr;
-    double2 *colpart = nullptr;  // symmetric fast kernel: reaction partial sums [nblocks][npad]
+    double2 *colpart = nullptr;  // symmetric fast kernel: reaction partial sums [owned blocks][npad]
+    double2 *vbuf = nullptr;     // symmetric fast kernel: per-virtual-rank force vectors [SYM_V][npad]
+    int v0 = 0, nv = SYM_V;      // virtual ranks owned by this shard
+    int nblocks_owned = 0;       // colpart slots (row blocks of the owned virtual ranks, whole groups)
     NcclComm comm = nullptr;
     cudaGraphExec_t graph[2] = {nullptr, nullptr};   // indexed by the starting slot
 };
@@ -142,6 +145,7 @@ static void free_shard(Shard &s)
     if (s.frc) cudaFree(s.frc);
     if (s.part) cudaFree(s.part);
     if (s.colpart) cudaFree(s.colpart);
+    if (s.vbuf) cudaFree(s.vbuf);
     if (s.ev0) cudaEventDestroy(s.ev0);
     if (s.ev1) cudaEventDestroy(s.ev1);
     if (s.comm) {
@@ -160,8 +164,10 @@ static ForceArgs force_args(const nbody_gpu *h, const Shard &s, int slot)
     a.out = (h->cfg.mode == NBODY_GPU_MODE_FAST) ? s.part : s.frc;
     a.n = h->n;
     a.npad = h->npad;
-    a.lo = s.lo;
-    a.hi = s.hi;
+    // symmetric kernel: every device holds the complete force vectors after the exchange and integrates
+    // ALL bodies (identical bits everywhere), which saves the position all-gather
+    a.lo = h->symmetric ? 0 : s.lo;
+    a.hi = h->symmetric ? h->n : s.hi;
     a.chunk = h->chunk;
     return a;
 }
@@ -175,18 +181,20 @@ static IntegrateArgs integrate_args(const nbody_gpu *h, const Shard &s, int slot
     a.vel = s.vel;
     a.frc = s.frc;
     a.part = s.part;
-    a.colpart = h->symmetric ? s.colpart : nullptr;
-    a.chunk = h->chunk;
+    a.vbuf = h->symmetric ? s.vbuf : nullptr;
     a.nsplit = h->nsplit;
     a.npad = h->npad;
-    a.lo = s.lo;
-    a.hi = s.hi;
+    // symmetric kernel: every device holds the complete force vectors after the exchange and integrates
+    // ALL bodies (identical bits everywhere), which saves the position all-gather
+    a.lo = h->symmetric ? 0 : s.lo;
+    a.hi = h->symmetric ? h->n : s.hi;
     a.xdim = h->cfg.xdim;
     a.ydim = h->cfg.ydim;
     return a;
 }
 
-// Enqueue the force kernel of shard s on the positions in slot `slot`.
+// Enqueue the force kernel of shard s on the positions in slot `slot` (for the symmetric kernel also
+// the fold of its partial sums into this device's virtual-rank vectors).
 static void enqueue_forces(nbody_gpu *h, Shard &s, int slot)
 {
     if (h->cfg.mode != NBODY_GPU_MODE_FAST) {
@@ -200,12 +208,27 @@ static void enqueue_forces(nbody_gpu *h, Shard &s, int slot)
         a.n = h->n;
         a.npad = h->npad;
         a.chunk = h->chunk;
-        a.block_first = 0;
-        a.block_stride = 1;
-        launch_forces_sym(a, h->nblocks, h->nsplit, s.stream);
+        a.v0 = s.v0;
+        a.nv = s.nv;
+        launch_forces_sym(a, s.nblocks_owned, h->nsplit, s.stream);
     } else {
         launch_forces_fast(force_args(h, s, slot), h->nsplit, s.stream);
     }
+}
+
+static void enqueue_sym_reduce(nbody_gpu *h, Shard &s)
+{
+    SymReduceArgs a;
+    a.rowpart = s.part;
+    a.colpart = s.colpart;
+    a.vbuf = s.vbuf;
+    a.n = h->n;
+    a.npad = h->npad;
+    a.chunk = h->chunk;
+    a.nsplit = h->nsplit;
+    a.v0 = s.v0;
+    a.nv = s.nv;
+    launch_sym_reduce(a, s.stream);
 }
 
 static void enqueue_integrate(nbody_gpu *h, Shard &s, int slot)
@@ -214,35 +237,94 @@ static void enqueue_integrate(nbody_gpu *h, Shard &s, int slot)
     else launch_integrate_exact(integrate_args(h, s, slot), s.stream);
 }
 
-// Enqueue the two kernels of one step on shard s, reading slot `slot`.
-static void enqueue_step_kernels(nbody_gpu *h, Shard &s, int slot)
-{
-    enqueue_forces(h, s, slot);
-    enqueue_integrate(h, s, slot);
-}
-
 }  // namespace nbody
 
 namespace nbody {
 
-// In-place all-gather of `buf` (npad double2, shard r's rows at [r*rows_per_shard, ...)) on every
-// local shard: replaces MPI_Allgatherv (reference nbody-par.c:913-917).
-static int allgather(nbody_gpu *h, int which /*0,1 = pos slot, 2 = vel, 3 = frc*/)
+enum { AG_POS0 = 0, AG_POS1 = 1, AG_VEL = 2, AG_FRC = 3, AG_VBUF = 4 };
+
+// In-place all-gather on every local shard.  Row arrays (npad double2, shard r's rows at
+// [r*rows_per_shard, ...)) replace MPI_Allgatherv (reference nbody-par.c:913-917); AG_VBUF gathers the
+// symmetric kernel's per-virtual-rank force vectors (shard r owns SYM_V/P consecutive ones).
+static int allgather(nbody_gpu *h, int which)
 {
     if (!h->sharded) return NBODY_GPU_OK;
     const char *why = "";
     const NcclApi *api = nccl_api(&why);
     if (!api) return fail(NBODY_GPU_ENCCL, "NCCL unavailable: %s", why);
-    const size_t count = static_cast<size_t>(h->rows_per_shard) * 2;   // doubles per shard
     const bool group = h->shards.size() > 1;
     if (group) NB_NCCL(api, api->GroupStart());
     for (Shard &s : h->shards) {
-        double2 *buf = which == 0 ? s.pos[0] : which == 1 ? s.pos[1] : which == 2 ? s.vel : s.frc;
-        const double2 *send = buf + static_cast<size_t>(s.part_index) * h->rows_per_shard;
-        NB_NCCL(api, api->AllGather(send, buf, count, NCCL_DOUBLE, s.comm, s.stream));
+        double2 *buf;
+        size_t per_shard;   // double2 elements contributed by each shard
+        if (which == AG_VBUF) {
+            buf = s.vbuf;
+            per_shard = static_cast<size_t>(s.nv) * h->npad;
+        } else {
+            buf = which == AG_POS0 ? s.pos[0] : which == AG_POS1 ? s.pos[1] : which == AG_VEL ? s.vel : s.frc;
+            per_shard = static_cast<size_t>(h->rows_per_shard);
+        }
+        const double2 *send = buf + static_cast<size_t>(s.part_index) * per_shard;
+        NB_NCCL(api, api->AllGather(send, buf, per_shard * 2, NCCL_DOUBLE, s.comm, s.stream));
     }
     if (group) NB_NCCL(api, api->GroupEnd());
     h->launches[3] += static_cast<long long>(h->shards.size());
+    return NBODY_GPU_OK;
+}
+
+// Optional per-phase event hooks for nbody_gpu_step_profiled: mark(shard index, phase 0..4).
+struct StepMarks {
+    virtual int mark(size_t shard, int phase) = 0;
+    virtual ~StepMarks() {}
+};
+
+// One step on every local shard, reading slot h->cur:
+//   forces [+ symmetric fold] | (symmetric & sharded: all-gather of the virtual-rank vectors)
+//   | integrate | (directed & sharded: all-gather of the new positions) | flip.
+// Phases for marks: 0 start, 1 after forces, 2 after fold, 3 after exchange A, 4 after integrate, 5 after exchange B.
+static int run_one_step(nbody_gpu *h, StepMarks *marks)
+{
+    const size_t nsh = h->shards.size();
+#define NB_MARK(phase)                                          \
+    if (marks) {                                                \
+        for (size_t k_ = 0; k_ < nsh; ++k_) {                   \
+            int rc_ = marks->mark(k_, phase);                   \
+            if (rc_) return rc_;                                \
+        }                                                       \
+    }
+    NB_MARK(0)
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        enqueue_forces(h, s, h->cur);
+    }
+    h->launches[0] += static_cast<long long>(nsh);
+    NB_MARK(1)
+    if (h->symmetric) {
+        for (Shard &s : h->shards) {
+            NB_CUDA(cudaSetDevice(s.device));
+            enqueue_sym_reduce(h, s);
+        }
+        h->launches[2] += static_cast<long long>(nsh);
+    }
+    NB_MARK(2)
+    if (h->symmetric) {
+        int rc = allgather(h, AG_VBUF);
+        if (rc) return rc;
+    }
+    NB_MARK(3)
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        enqueue_integrate(h, s, h->cur);
+    }
+    h->launches[1] += static_cast<long long>(nsh);
+    NB_MARK(4)
+    if (!h->symmetric) {
+        int rc = allgather(h, h->cur ^ 1);
+        if (rc) return rc;
+    }
+    NB_MARK(5)
+#undef NB_MARK
+    h->cur ^= 1;   // the reference's world->old ^= 1 (nbody-seq.c:464)
     return NBODY_GPU_OK;
 }
 
@@ -266,7 +348,9 @@ static int build_graph(nbody_gpu *h, Shard &s, int start_slot)
     NB_CUDA(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
     int slot = start_slot;
     for (int k = 0; k < h->graph_steps; ++k) {
-        enqueue_step_kernels(h, s, slot);
+        enqueue_forces(h, s, slot);
+        if (h->symmetric) enqueue_sym_reduce(h, s);
+        enqueue_integrate(h, s, slot);
         slot ^= 1;
     }
     cudaError_t e = cudaStreamEndCapture(s.stream, &g);
@@ -301,19 +385,13 @@ static int do_steps(nbody_gpu *h, int steps)
             NB_CUDA(cudaGraphLaunch(s.graph[h->cur], s.stream));
             h->launches[0] += h->graph_steps;
             h->launches[1] += h->graph_steps;
+            if (h->symmetric) h->launches[2] += h->graph_steps;
             left -= h->graph_steps;   // graph_steps is even: h->cur is unchanged
         }
     }
     for (; left > 0; --left) {
-        for (Shard &s : h->shards) {
-            NB_CUDA(cudaSetDevice(s.device));
-            enqueue_step_kernels(h, s, h->cur);
-        }
-        h->launches[0] += static_cast<long long>(h->shards.size());
-        h->launches[1] += static_cast<long long>(h->shards.size());
-        int rc = allgather(h, h->cur ^ 1);
+        int rc = run_one_step(h, nullptr);
         if (rc) return rc;
-        h->cur ^= 1;   // the reference's world->old ^= 1 (nbody-seq.c:464)
     }
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
@@ -395,7 +473,7 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
     h->sharded = P > 1;
     h->rows_per_shard = (h->n + P - 1) / P;
     h->npad = h->rows_per_shard * P;
-    h->symmetric = cfg->mode == NBODY_GPU_MODE_FAST && !h->sharded &&
+    h->symmetric = cfg->mode == NBODY_GPU_MODE_FAST && (SYM_V % P == 0) &&
                    (cfg->symmetric > 0 || (cfg->symmetric == 0 && h->n >= 8192));
     h->nblocks = (h->n + SYM_RB - 1) / SYM_RB;
     if (h->symmetric) choose_split_sym(h->n, cfg->jsplit, &h->nsplit, &h->chunk);
@@ -432,8 +510,16 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
             NB_CUDA(cudaMalloc(&s.part, bytes * h->nsplit));
             NB_CUDA(cudaMemsetAsync(s.part, 0, bytes * h->nsplit, s.stream));
             if (h->symmetric) {
-                NB_CUDA(cudaMalloc(&s.colpart, bytes * h->nblocks));
-                NB_CUDA(cudaMemsetAsync(s.colpart, 0, bytes * h->nblocks, s.stream));
+                s.nv = SYM_V / P;
+                s.v0 = s.part_index * s.nv;
+                // colpart slots = grid.x of the force kernel: whole groups of 2*SYM_V row blocks; slots whose
+                // block lies beyond the last body exit at once
+                const size_t slots = static_cast<size_t>((h->nblocks + 2 * SYM_V - 1) / (2 * SYM_V)) * 2 * s.nv;
+                s.nblocks_owned = static_cast<int>(slots);
+                NB_CUDA(cudaMalloc(&s.colpart, bytes * slots));
+                NB_CUDA(cudaMemsetAsync(s.colpart, 0, bytes * slots, s.stream));
+                NB_CUDA(cudaMalloc(&s.vbuf, bytes * SYM_V));
+                NB_CUDA(cudaMemsetAsync(s.vbuf, 0, bytes * SYM_V, s.stream));
             }
         }
     }
@@ -537,73 +623,74 @@ int nbody_gpu_step_timed(nbody_gpu *h, int steps, float *ms)
     return NBODY_GPU_OK;
 }
 
+namespace {
+struct EventMarks : StepMarks {
+    nbody_gpu *h;
+    std::vector<cudaEvent_t> ev;   // [shard][step][phase 0..5]
+    int steps, step = 0;
+    EventMarks(nbody_gpu *h_, int steps_) : h(h_), ev(h_->shards.size() * static_cast<size_t>(steps_) * 6, nullptr), steps(steps_) {}
+    cudaEvent_t &at(size_t k, int st, int phase) { return ev[(k * steps + st) * 6 + phase]; }
+    int mark(size_t k, int phase) override
+    {
+        NB_CUDA(cudaSetDevice(h->shards[k].device));
+        NB_CUDA(cudaEventRecord(at(k, step, phase), h->shards[k].stream));
+        return NBODY_GPU_OK;
+    }
+};
+}  // namespace
+
 int nbody_gpu_step_profiled(nbody_gpu *h, int steps, int flush_l2, float out_ms[4])
 {
     if (!h || !out_ms || steps < 0) return fail(NBODY_GPU_EINVAL, "bad argument");
     int rc = sync_all(h);
     if (rc) return rc;
+    for (int q = 0; q < 4; ++q) out_ms[q] = 0.f;
+    if (steps == 0) return NBODY_GPU_OK;
     const size_t flush_bytes = 256u << 20;
     const size_t nsh = h->shards.size();
-    // events: per shard, per step: t0 (before force), t1 (after force), t2 (after integrate), t3 (after exchange)
-    std::vector<cudaEvent_t> ev(nsh * (static_cast<size_t>(steps) * 4 + 2), nullptr);
+    EventMarks marks(h, steps);
     std::vector<void *> scratch(nsh, nullptr);
-    auto E = [&](size_t k, int step, int which) -> cudaEvent_t & {
-        return ev[k * (static_cast<size_t>(steps) * 4 + 2) + static_cast<size_t>(step) * 4 + which];
-    };
     for (size_t k = 0; k < nsh; ++k) {
         NB_CUDA(cudaSetDevice(h->shards[k].device));
-        for (size_t e = 0; e < static_cast<size_t>(steps) * 4 + 2; ++e)
-            NB_CUDA(cudaEventCreate(&ev[k * (static_cast<size_t>(steps) * 4 + 2) + e]));
+        for (int st = 0; st < steps; ++st)
+            for (int ph = 0; ph < 6; ++ph) NB_CUDA(cudaEventCreate(&marks.at(k, st, ph)));
         if (flush_l2) NB_CUDA(cudaMalloc(&scratch[k], flush_bytes));
-    }
-    const int last = steps * 4;   // index of the two span events: E(k, steps, 0) and E(k, steps, 1)
-    (void)last;
-    for (size_t k = 0; k < nsh; ++k) {
-        NB_CUDA(cudaSetDevice(h->shards[k].device));
-        NB_CUDA(cudaEventRecord(E(k, steps, 0), h->shards[k].stream));
+        NB_CUDA(cudaEventRecord(h->shards[k].ev0, h->shards[k].stream));
     }
     for (int st = 0; st < steps; ++st) {
-        for (size_t k = 0; k < nsh; ++k) {
-            Shard &s = h->shards[k];
-            NB_CUDA(cudaSetDevice(s.device));
-            if (flush_l2) NB_CUDA(cudaMemsetAsync(scratch[k], st & 0xff, flush_bytes, s.stream));
-            NB_CUDA(cudaEventRecord(E(k, st, 0), s.stream));
-            enqueue_forces(h, s, h->cur);
-            NB_CUDA(cudaEventRecord(E(k, st, 1), s.stream));
-            enqueue_integrate(h, s, h->cur);
-            NB_CUDA(cudaEventRecord(E(k, st, 2), s.stream));
+        if (flush_l2) {
+            for (size_t k = 0; k < nsh; ++k) {
+                NB_CUDA(cudaSetDevice(h->shards[k].device));
+                NB_CUDA(cudaMemsetAsync(scratch[k], st & 0xff, flush_bytes, h->shards[k].stream));
+            }
         }
-        h->launches[0] += static_cast<long long>(nsh);
-        h->launches[1] += static_cast<long long>(nsh);
-        rc = allgather(h, h->cur ^ 1);
+        marks.step = st;
+        rc = run_one_step(h, &marks);
         if (rc) return rc;
-        for (size_t k = 0; k < nsh; ++k) {
-            NB_CUDA(cudaSetDevice(h->shards[k].device));
-            NB_CUDA(cudaEventRecord(E(k, st, 3), h->shards[k].stream));
-        }
-        h->cur ^= 1;
     }
     for (size_t k = 0; k < nsh; ++k) {
         NB_CUDA(cudaSetDevice(h->shards[k].device));
-        NB_CUDA(cudaEventRecord(E(k, steps, 1), h->shards[k].stream));
+        NB_CUDA(cudaEventRecord(h->shards[k].ev1, h->shards[k].stream));
     }
-    for (int q = 0; q < 4; ++q) out_ms[q] = 0.f;
     for (size_t k = 0; k < nsh; ++k) {
-        NB_CUDA(cudaSetDevice(h->shards[k].device));
-        NB_CUDA(cudaEventSynchronize(E(k, steps, 1)));
+        Shard &s = h->shards[k];
+        NB_CUDA(cudaSetDevice(s.device));
+        NB_CUDA(cudaEventSynchronize(s.ev1));
         float acc[4] = {0.f, 0.f, 0.f, 0.f}, t = 0.f;
-        NB_CUDA(cudaEventElapsedTime(&acc[0], E(k, steps, 0), E(k, steps, 1)));
+        NB_CUDA(cudaEventElapsedTime(&acc[0], s.ev0, s.ev1));
         for (int st = 0; st < steps; ++st) {
-            for (int q = 0; q < 3; ++q) {
-                NB_CUDA(cudaEventElapsedTime(&t, E(k, st, q), E(k, st, q + 1)));
-                acc[q + 1] += t;
+            // phases: 0-1 force kernel | 1-2 symmetric fold | 2-3 exchange A | 3-4 integrate | 4-5 exchange B
+            static const int bucket[5] = {1, 2, 3, 2, 3};
+            for (int ph = 0; ph < 5; ++ph) {
+                NB_CUDA(cudaEventElapsedTime(&t, marks.at(k, st, ph), marks.at(k, st, ph + 1)));
+                acc[bucket[ph]] += t;
             }
         }
         if (!h->sharded) acc[3] = 0.f;
         for (int q = 0; q < 4; ++q)
             if (acc[q] > out_ms[q]) out_ms[q] = acc[q];
-        for (size_t e = 0; e < static_cast<size_t>(steps) * 4 + 2; ++e)
-            cudaEventDestroy(ev[k * (static_cast<size_t>(steps) * 4 + 2) + e]);
+        for (int st = 0; st < steps; ++st)
+            for (int ph = 0; ph < 6; ++ph) cudaEventDestroy(marks.at(k, st, ph));
         if (scratch[k]) cudaFree(scratch[k]);
         NB_CUDA(cudaGetLastError());
     }
@@ -634,14 +721,21 @@ int nbody_gpu_forces(nbody_gpu *h, double *xf, double *yf)
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
         enqueue_forces(h, s, h->cur);
-        if (h->cfg.mode == NBODY_GPU_MODE_FAST) {
-            launch_reduce_fast(integrate_args(h, s, h->cur), s.stream);
-            h->launches[2] += 1;
-        }
+        if (h->symmetric) enqueue_sym_reduce(h, s);
         h->launches[0] += 1;
         NB_CUDA(cudaGetLastError());
     }
-    int rc = allgather(h, 3);
+    int rc = NBODY_GPU_OK;
+    if (h->symmetric) rc = allgather(h, AG_VBUF);
+    if (rc) return rc;
+    if (h->cfg.mode == NBODY_GPU_MODE_FAST) {
+        for (Shard &s : h->shards) {
+            NB_CUDA(cudaSetDevice(s.device));
+            launch_reduce_fast(integrate_args(h, s, h->cur), s.stream);   // partial sums -> frc
+            h->launches[2] += 1;
+        }
+    }
+    if (!h->symmetric) rc = allgather(h, AG_FRC);
     if (rc) return rc;
     Shard &s0 = h->shards[0];
     NB_CUDA(cudaSetDevice(s0.device));
@@ -654,11 +748,11 @@ int nbody_gpu_fetch(nbody_gpu *h, double *x, double *y, double *xf, double *yf, 
 {
     if (!h) return fail(NBODY_GPU_EINVAL, "handle is NULL");
     int rc = NBODY_GPU_OK;
-    if (h->sharded) {
+    if (h->sharded && !h->symmetric) {
         // forces and velocities live sharded during the run; gather them like the reference's
         // whole-struct MPI_Allgatherv leaves them (nbody-par.c:933-936)
-        if (xv || yv) rc = allgather(h, 2);
-        if (!rc && (xf || yf)) rc = allgather(h, 3);
+        if (xv || yv) rc = allgather(h, AG_VEL);
+        if (!rc && (xf || yf)) rc = allgather(h, AG_FRC);
         if (rc) return rc;
     }
     Shard &s0 = h->shards[0];
@@ -674,6 +768,27 @@ int nbody_gpu_fetch(nbody_gpu *h, double *x, double *y, double *xf, double *yf, 
         NB_CUDA(cudaGetLastError());
     }
     return NBODY_GPU_OK;
+}
+
+int nbody_gpu_describe(const nbody_gpu *h, char *buf, int len)
+{
+    if (!h) return 0;
+    const bool fast = h->cfg.mode == NBODY_GPU_MODE_FAST;
+    const char *kernel = !fast ? "forces_kernel<EXACT>" : h->symmetric ? "forces_sym_kernel<128,4>" : "forces_fast_kernel<2,4,1,true>";
+    // FP64-pipe instructions per directed pair-interaction (SASS counts): the symmetric
+    // kernel issues 19 per unordered pair = 2 interactions; exact mode is not a fixed count (divisions, branches)
+    const double ipp = !fast ? 0.0 : h->symmetric ? 9.5 : 16.0;
+    char tmp[512];
+    const int need = snprintf(tmp, sizeof tmp,
+                              "{\"mode\": \"%s\", \"kernel\": \"%s\", \"symmetric\": %s, \"nsplit\": %d, \"chunk\": %d, "
+                              "\"row_blocks\": %d, \"shards\": %d, \"graph_steps\": %d, \"fp64_instr_per_pair\": %.1f}",
+                              fast ? "fast" : "exact", kernel, h->symmetric ? "true" : "false", h->nsplit, h->chunk,
+                              h->symmetric ? h->nblocks : 0, h->nshards_total, h->sharded ? 0 : h->graph_steps, ipp);
+    if (buf && len > 0) {
+        strncpy(buf, tmp, static_cast<size_t>(len) - 1);
+        buf[len - 1] = 0;
+    }
+    return need + 1;
 }
 
 long long nbody_gpu_launch_count(const nbody_gpu *h, long long out[4])

@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 #include <cstddef>
+#include <cstdlib>
 
 namespace nbody {
 
@@ -36,6 +37,13 @@ inline const NcclApi *nccl_api(const char **why)
     static const char *err = "";
     if (!tried) {
         tried = true;
+        // stdout belongs to the caller (the host driver prints the final state there): NCCL's own
+        // banner/debug lines (NCCL_DEBUG=VERSION|INFO) go to stderr unless the user chose a file
+        // (NCCL honours NCCL_DEBUG_FILE only above the VERSION level, so VERSION is raised to WARN,
+        // which prints the same banner)
+        const char *dbg = getenv("NCCL_DEBUG");
+        if (dbg && (dbg[0] == 'V' || dbg[0] == 'v')) setenv("NCCL_DEBUG", "WARN", 1);
+        setenv("NCCL_DEBUG_FILE", "/dev/stderr", 0);
         const char *names[] = {"libnccl.so.2", "libnccl.so"};
         for (const char *nm : names) {
             api.lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);

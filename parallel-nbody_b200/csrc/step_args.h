@@ -32,8 +32,43 @@ struct SymArgs {
     int n;
     int npad;
     int chunk;            // j-chunk length, a multiple of SYM_RB
-    int block_first;      // this launch handles row blocks block_first + k*block_stride, k = 0..grid.x-1
-    int block_stride;
+    int v0, nv;           // this device owns the row blocks B with (B % SYM_V) in [v0, v0+nv): "virtual ranks"
+};
+
+// The symmetric kernel's partial sums are combined through SYM_V fixed "virtual ranks": row block B
+// belongs to virtual rank sym_vrank(B); vbuf[v][j] = reactions on j from v's blocks below block(j)
+// (B ascending) + (if block(j) belongs to v) j's own row sums (chunk ascending); F(j) = sum over
+// v = 0..SYM_V-1 of vbuf[v][j].  A device owns SYM_V/P consecutive virtual ranks, so the sum --
+// and therefore every bit of the result -- is the same for P = 1, 2, 4, 8 GPUs.
+constexpr int SYM_V = 8;
+
+// Row block -> virtual rank, boustrophedon over groups of 2*SYM_V blocks (0..7 then 7..0): block B's work
+// falls linearly with B, so every virtual rank gets the same share and any split of the virtual ranks over
+// GPUs is balanced.
+__host__ __device__ inline int sym_vrank(int B)
+{
+    const int r = B % (2 * SYM_V);
+    return r < SYM_V ? r : 2 * SYM_V - 1 - r;
+}
+// local slot of row block B in a device's colpart array (device owns virtual ranks [v0, v0+nv))
+__host__ __device__ inline int sym_local_block(int B, int v0, int nv)
+{
+    const int r = B % (2 * SYM_V);
+    const int half = r < SYM_V ? 0 : 1;
+    return (B / (2 * SYM_V)) * 2 * nv + half * nv + (sym_vrank(B) - v0);
+}
+// inverse: k-th owned block (ascending B within each virtual rank)
+__host__ __device__ inline int sym_owned_block(int k, int v0, int nv)
+{
+    const int g = k / (2 * nv), r = k % (2 * nv);
+    return r < nv ? g * 2 * SYM_V + v0 + r : g * 2 * SYM_V + 2 * SYM_V - 1 - (v0 + r - nv);
+}
+struct SymReduceArgs {
+    const double2 *rowpart;
+    const double2 *colpart;
+    double2 *vbuf;        // [SYM_V][npad]
+    int n, npad, chunk, nsplit;
+    int v0, nv;
 };
 
 struct IntegrateArgs {
@@ -43,8 +78,7 @@ struct IntegrateArgs {
     double2 *vel;
     double2 *frc;          // FAST: written (sum of partials); EXACT: read
     const double2 *part;   // FAST: partial sums (row side)
-    const double2 *colpart;  // FAST symmetric: reaction partial sums, else nullptr
-    int chunk;             // FAST symmetric: j-chunk length
+    const double2 *vbuf;   // FAST symmetric: [SYM_V][npad] per-virtual-rank sums (see SymReduceArgs), else nullptr
     int nsplit;            // FAST: number of j-chunks
     int npad;
     int lo, hi;
@@ -58,5 +92,6 @@ void launch_forces_fast(const ForceArgs &a, int nsplit, cudaStream_t st);
 void launch_integrate_fast(const IntegrateArgs &a, cudaStream_t st);
 void launch_reduce_fast(const IntegrateArgs &a, cudaStream_t st);
 int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream_t st);   // returns cudaError_t
+void launch_sym_reduce(const SymReduceArgs &a, cudaStream_t st);
 
 }  // namespace nbody

@@ -243,23 +243,22 @@ __device__ __forceinline__ void integrate_body(const IntegrateArgs &a, int i, do
     a.pos_new[i] = make_double2(xn, yn);
 }
 
-// FAST: total force on body i from the partial sums, in a fixed order: reactions from lower row
-// blocks (block index ascending) first, then the row-side j-chunks (ascending) -- lower j first,
-// like the reference's loop.  Directed kernel: colpart == nullptr, all chunks are row-side.
+// FAST: total force on body i from the partial sums, in a fixed order.  Directed kernel: the j-chunk
+// partials, chunk ascending.  Symmetric kernel: the per-virtual-rank vectors of sym_reduce_kernel.
 __device__ __forceinline__ void sum_partials(const IntegrateArgs &a, int i, double &xf, double &yf)
 {
     xf = 0.0;
     yf = 0.0;
-    int s0 = 0;
-    if (a.colpart) {
-        const int blk = i / SYM_RB;
-        for (int b = 0; b < blk; ++b) {
-            const double2 t = a.colpart[static_cast<size_t>(b) * a.npad + i];
+    if (a.vbuf) {   // symmetric kernel: SYM_V per-virtual-rank sums, v ascending
+#pragma unroll
+        for (int v = 0; v < SYM_V; ++v) {
+            const double2 t = a.vbuf[static_cast<size_t>(v) * a.npad + i];
             xf += t.x;
             yf += t.y;
         }
-        s0 = (blk * SYM_RB) / a.chunk;
+        return;
     }
+    const int s0 = 0;
     for (int s = s0; s < a.nsplit; ++s) {
         const double2 t = a.part[static_cast<size_t>(s) * a.npad + i];
         xf += t.x;

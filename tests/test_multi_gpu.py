@@ -30,6 +30,34 @@ def test_sharded_equals_single_gpu_bits(nb, oracle, mode, n, steps):
             assert np.array_equal(a.view(np.uint64), c.view(np.uint64)), (mode, n, p)
 
 
+@pytest.mark.parametrize("n,steps", [(3000, 5), (20000, 2), (777, 6)])
+def test_symmetric_kernel_same_bits_on_1_2_4_8_gpus(nb, oracle, n, steps):
+    """The symmetric fast kernel sums its partial results through 8 fixed virtual ranks, so the bits do
+    not depend on how many GPUs (1, 2, 4 or 8) share them; other GPU counts use the directed kernel."""
+    k = nb.device_count()
+    if k < 2:
+        pytest.skip("needs >= 2 GPUs")
+    b = oracle.init_bodies(n)
+    b.x[n - 1], b.y[n - 1] = b.x[1], b.y[1]          # a coincident pair across row blocks
+    def run(p):
+        g = nb.NBodyGPU(b.x, b.y, b.xv, b.yv, b.mass, b.radius, mode=1, ngpus=p, symmetric=1)
+        g.step(steps)
+        out = g.fetch()
+        g.close()
+        return out
+    ref = run(1)
+    chk = b.copy()
+    oracle.run(chk, steps, trig=0, threads=8)
+    np.testing.assert_allclose(ref[0], chk.x, rtol=1e-12, atol=1e-12)
+    np.testing.assert_allclose(ref[4], chk.xv, rtol=1e-10, atol=1e-12)
+    for p in (2, 4, 8):
+        if p > k:
+            continue
+        got = run(p)
+        for a, c in zip(ref, got):
+            assert np.array_equal(a.view(np.uint64), c.view(np.uint64)), (n, p)
+
+
 def test_sharded_exact_matches_oracle_and_golden(nb, oracle):
     k = nb.device_count()
     if k < 2:
