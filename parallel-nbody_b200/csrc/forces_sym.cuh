@@ -84,13 +84,13 @@ __device__ __forceinline__ double warp_sum(double v)
     return v;
 }
 
-template <int IB, bool GUARD>
+template <int IB, bool GUARD, int UNROLL>
 __device__ __forceinline__ void sym_group(SymBody (&b)[IB], const double2 *tp, const double2 *tm, int g, int cnt,
                                           int lane, double2 *col)
 {
     double cx = 0.0, cy = 0.0;
     const int src = (lane + 1) & 31;
-#pragma unroll 4
+#pragma unroll UNROLL
     for (int r = 0; r < 32; ++r) {
         const int jj = g + ((lane + r) & 31);
         double2 pj, qj;
@@ -144,8 +144,8 @@ __device__ __noinline__ double sym_col_rescan(const double2 *pos, const double2 
     return c;
 }
 
-template <int SYM_THREADS, int SYM_IB>
-__global__ void __launch_bounds__(SYM_THREADS) forces_sym_kernel(const SymArgs a)
+template <int SYM_THREADS, int SYM_IB, int MINB = 1, int UNROLL = 4>
+__global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const SymArgs a)
 {
     static_assert(SYM_RB == SYM_THREADS * SYM_IB, "row block = threads x bodies per thread");
     constexpr int SYM_WARPS = SYM_THREADS / 32;
@@ -232,9 +232,9 @@ __global__ void __launch_bounds__(SYM_THREADS) forces_sym_kernel(const SymArgs a
             // exactly once and after 32 steps lane l holds the warp's complete reaction sum for j = g + l:
             // no reduction tree, no atomics, fixed order.
             if (cnt == TILE_J) {
-                for (int g = 0; g < TILE_J; g += 32) sym_group<SYM_IB, false>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J);
+                for (int g = 0; g < TILE_J; g += 32) sym_group<SYM_IB, false, UNROLL>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J);
             } else {
-                for (int g = 0; g < cnt; g += 32) sym_group<SYM_IB, true>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J);
+                for (int g = 0; g < cnt; g += 32) sym_group<SYM_IB, true, UNROLL>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J);
             }
             bool hit = false;
 #pragma unroll

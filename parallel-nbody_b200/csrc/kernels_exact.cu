@@ -1,7 +1,10 @@
 // kernels_exact.cu -- EXACT-mode instantiations.  Build with -fmad=false (see Makefile):
 // bit-identical to reference nbody-seq.c compiled without FMA contraction and linked
 // against include/nbody_detmath.h (oracle/_ref/nbody-seq-det-hex).
+#include <cstdlib>
+
 #include "step_kernels.cuh"
+#include "forces_exact_wide.cuh"
 
 namespace nbody {
 
@@ -9,8 +12,15 @@ void launch_forces_exact(const ForceArgs &a, cudaStream_t st)
 {
     const int rows = a.hi - a.lo;
     if (rows <= 0) return;
-    dim3 grid((rows + FORCE_THREADS - 1) / FORCE_THREADS, 1);
-    forces_kernel<MODE_EXACT><<<grid, FORCE_THREADS, 0, st>>>(a);
+    // development knob: NBODY_EXACT_VARIANT=1 selects the one-thread-per-body kernel (same bits)
+    static const int variant = getenv("NBODY_EXACT_VARIANT") ? atoi(getenv("NBODY_EXACT_VARIANT")) : 0;
+    if (variant == 1) {
+        dim3 grid((rows + FORCE_THREADS - 1) / FORCE_THREADS, 1);
+        forces_kernel<MODE_EXACT><<<grid, FORCE_THREADS, 0, st>>>(a);
+        return;
+    }
+    cudaFuncSetAttribute(forces_exact_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EXW_SMEM_BYTES);
+    forces_exact_wide_kernel<<<(rows + EXW_ROWS - 1) / EXW_ROWS, EXW_THREADS, EXW_SMEM_BYTES, st>>>(a);
 }
 
 void launch_integrate_exact(const IntegrateArgs &a, cudaStream_t st)

@@ -46,11 +46,22 @@ int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream
     static const int variant = getenv("NBODY_SYM_VARIANT") ? atoi(getenv("NBODY_SYM_VARIANT")) : 0;
     dim3 grid(nblocks_here, nsplit);
     cudaError_t e;
-#define NB_SYM_LAUNCH(T, IB)                                                                                       \
-    e = cudaFuncSetAttribute(forces_sym_kernel<T, IB>, cudaFuncAttributeMaxDynamicSharedMemorySize, sym_smem_bytes(T)); \
+#define NB_SYM_LAUNCH(...)                                                                                          \
+    e = cudaFuncSetAttribute(forces_sym_kernel<__VA_ARGS__>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);    \
     if (e != cudaSuccess) return static_cast<int>(e);                                                              \
-    forces_sym_kernel<T, IB><<<grid, T, sym_smem_bytes(T), st>>>(a);
-    if (variant == 1) { NB_SYM_LAUNCH(256, 2) } else { NB_SYM_LAUNCH(128, 4) }
+    forces_sym_kernel<__VA_ARGS__><<<grid, threads, smem, st>>>(a);
+    int threads = 128;
+    if (variant == 1) threads = 256;
+    const int smem = sym_smem_bytes(threads);
+    switch (variant) {
+    default: NB_SYM_LAUNCH(128, 4) break;
+    case 1: NB_SYM_LAUNCH(256, 2) break;
+    case 2: NB_SYM_LAUNCH(128, 4, 5) break;
+    case 3: NB_SYM_LAUNCH(128, 4, 6) break;
+    case 4: NB_SYM_LAUNCH(128, 4, 1, 2) break;
+    case 5: NB_SYM_LAUNCH(128, 4, 1, 8) break;
+    case 6: NB_SYM_LAUNCH(128, 4, 5, 2) break;
+    }
 #undef NB_SYM_LAUNCH
     return 0;
 }
