@@ -6,8 +6,8 @@
 
 Workload (BASELINE.json config 4, the one `metric` is quoted on): N = 262144 bodies from the
 reference initialiser (srand(27102015), world 1024x768; reference nbody/nbody-par.c:208-222),
-fast mode, STRONG scaling: the same 262144 bodies are row-sharded over the GPUs and the new
-positions are all-gathered every step (ncclAllGather replaces MPI_Allgatherv, nbody-par.c:913).
+fast mode, STRONG scaling: the same 262144 bodies are sharded over the GPUs (row blocks of the symmetric
+kernel) and one ncclAllGather per step replaces MPI_Allgatherv (nbody-par.c:913).
 A step = one force + integrate (+ exchange) pass.  value = K * N * (N-1) / t, t = device time of
 the K-step loop (CUDA events on the library's stream), max over ranks.
 
@@ -20,8 +20,8 @@ directed pair-interaction) / the kernel's mean duration from per-launch CUDA eve
 timed region; peak = the DFMA rate measured live by nbody_gpu_fp64_peak (MEASURED_PEAKS.json has
 no FP64 figure).  pipe_frac = FP64-pipe instructions actually issued per pair (SASS count,
 confirmed by ncu sm__inst_executed_pipe_fp64) x pairs/s / (peak/2): the utilisation figure the
-north star's "% of FP64 pipe peak" means (IEEE-grade rsqrt makes one pair ~19 pipe instructions,
-so the algorithmic-flop fraction cannot approach 1).
+north star's "% of FP64 pipe peak" means (an IEEE-grade rsqrt makes one unordered pair 19 pipe
+instructions = 9.5 per interaction, so the algorithmic-flop fraction cannot approach 1).
 
 --impl reference: the reference's CPU algorithm (oracle port, libm trig, row form = nbody-par's
 pass B, nbody-par.c:302-308) on all host cores, each step a bounded sample of rows of the same
