@@ -151,6 +151,35 @@ def cpu_seq_sample(oracle_lib, b, n, budget_s):
     return 2.0 * ev / dt, rows2, dt
 
 
+def reference_binary_check(n_small=16384, steps=2):
+    """The reference's OWN parallel program (unmodified nbody-par.c built by oracle/Makefile against the
+    fork/shared-memory MPI stand-in; MAXBODIES raised) on all host cores, pure MPI (one rank per core), at a
+    size it finishes in seconds.  Per-pair cost does not depend on N, so this pins the port's rate to the real
+    thing.  Returns None if oracle/_ref/nbody-par-big is not built."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "nbody-par-big")
+    if not os.path.exists(exe):
+        return None
+    import tempfile
+    import oracle_lib
+    cores = os.cpu_count() or 1
+    with tempfile.TemporaryDirectory() as d:
+        ppm = os.path.join(d, "nbody.ppm")
+        oracle_lib.write_ppm(ppm, XDIM, YDIM)
+        env = dict(os.environ, MPISHIM_NP=str(cores), OMP_NUM_THREADS="1")
+        try:
+            r = subprocess.run([exe, str(n_small), "0", ppm, str(steps)], env=env, cwd=d, stdout=subprocess.DEVNULL,
+                               stderr=subprocess.PIPE, text=True, timeout=300)
+        except (OSError, subprocess.TimeoutExpired):
+            return None
+    took = [ln for ln in r.stderr.splitlines() if "N-body took" in ln]
+    if r.returncode != 0 or not took:
+        return None
+    secs = float(took[0].split(":")[1].split()[0])
+    return {"kind": "reference", "binary": "oracle/_ref/nbody-par-big (reference nbody-par.c + MPI stand-in)",
+            "ranks": cores, "threads_per_rank": 1, "n": n_small, "steps": steps, "seconds": secs,
+            "value": steps * n_small * (n_small - 1.0) / max(secs, 1e-9), "unit": UNIT}
+
+
 def run_reference(args, rank, world):
     """The reference arm: CPU only, rank 0 only."""
     if rank != 0:
@@ -192,6 +221,9 @@ def run_reference(args, rank, world):
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
             "note": "ms_per_step is the sample time scaled to a full step (x N/rows)"}
+    chk = reference_binary_check()
+    if chk:
+        line["cpu_baseline"]["reference_check"] = chk
     print(json.dumps(line), flush=True)
 
 
@@ -315,6 +347,10 @@ def main():
                "seq_1core": {"value": v1, "cores": 1,
                              "sample": "triangular walk rows [0,%d) (nbody-seq form, 2 interactions per evaluation), "
                                        "%.1f s" % (rws1, dt1)}}
+
+        chk = reference_binary_check()
+        if chk:
+            cpu["reference_check"] = chk
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": t_ms / args.steps, "higher_is_better": True,

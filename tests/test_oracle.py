@@ -106,3 +106,24 @@ def test_flop_model(oracle):
     # nbody-seq.c:367-380
     assert oracle.lib().oracle_nr_flops(128, 1000) == 1000 * (20 * (128 * 127 // 2) + 22 * 128)
     assert oracle.lib().oracle_nr_flops(262144, 50) == 50 * (20 * (262144 * 262143 // 2) + 22 * 262144)
+
+
+@pytest.mark.parametrize("ranks,threads,flag", [(1, 1, None), (2, 1, None), (3, 2, "--openmp"), (8, 1, None)])
+def test_reference_nbody_par_reproduces_goldens(oracle, ppm, ranks, threads, flag):
+    """The reference's parallel program (unmodified nbody-par.c + the MPI stand-in of oracle/mpi_shim) is a
+    text-level oracle: any rank count, with and without --openmp, prints the golden state (its bits differ
+    from nbody-seq's because the summation order depends on the partition, SURVEY section 0 point 5)."""
+    exe = oracle.ref_binary("nbody-par")
+    if exe is None:
+        pytest.skip("oracle/_ref/nbody-par not built")
+    env = dict(os.environ, MPISHIM_NP=str(ranks), OMP_NUM_THREADS=str(threads))
+    for n, steps, name in ((128, 1000, "128_MY_REF_OUTPUT_128x1000.txt"), (32, 20000, None)):
+        cmd = [exe, str(n), "0", ppm, str(steps)] + ([flag] if flag else [])
+        out = subprocess.run(cmd, check=True, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert b"took" in out.stderr
+        if name:
+            assert out.stdout.decode() == oracle.golden_text(name)
+        else:
+            b = oracle.init_bodies(n)
+            oracle.run(b, steps, trig=0)
+            assert out.stdout.decode() == oracle.format_state(b.x, b.y, b.xf, b.yf, b.xv, b.yv)
