@@ -118,6 +118,10 @@ NBODY_DM_FN double nbody_dm_atan2(double y, double x, const double *tab)
     int k = 0;
     double p = 0.0;
     if (b > 0.0) {
+        if (b < 0x1p-900) {   /* subnormal neighbourhood: scale up (exact) so the ratio estimate sees normal numbers */
+            a = NBODY_DM_MUL(a, 0x1p200);
+            b = NBODY_DM_MUL(b, 0x1p200);
+        }
         k = nbody_dm_atan_index(a, b);
         double c = NBODY_DM_MUL((double)k, 0.125);
         double num = NBODY_DM_SUB(a, NBODY_DM_MUL(c, b));

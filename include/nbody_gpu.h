@@ -108,6 +108,12 @@ int nbody_gpu_forces(nbody_gpu *h, double *xf, double *yf);
 int nbody_gpu_fetch(nbody_gpu *h, double *x, double *y, double *xf, double *yf,
                     double *xv, double *yv);
 
+/* Replaces display() (nbody-seq.c:326-354; dead code in nbody-par.c:674-702): paints the CURRENT positions
+ * into rgb (xdim*ydim*3 bytes, host, row-major, 3 bytes per pixel): the first (lowest-index) body whose
+ * disc of radius R+0.5 covers the pixel gives the tint, empty space is black.  Headless: a device buffer,
+ * copied to the host; the driver writes it behind the P6 header when secs_per_update > 0. */
+int nbody_gpu_render(nbody_gpu *h, unsigned char *rgb);
+
 int nbody_gpu_sync(nbody_gpu *h);
 void nbody_gpu_destroy(nbody_gpu *h);
 

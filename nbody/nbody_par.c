@@ -15,8 +15,9 @@
  * the flop count is 64-bit, and the step loop runs on the GPU(s) behind the C ABI -- there is
  * no CPU step loop in this program.  Extra options, all after the four positionals so the
  * reference's parser would ignore them too: --gpus K (or env NBODY_GPUS), --mode exact|fast
- * (or env NBODY_MODE; default exact), --hex (print the state with %a instead of %10.3f).
- * secs_per_update is parsed and ignored, as in nbody-par (display() is dead code there).
+ * (or env NBODY_MODE; default exact), --hex (print the state with %a instead of %10.3f),
+ * --display-final (paint the final state into the PPM).  secs_per_update > 0 restores the timed
+ * display() of nbody-seq (nbody-seq.c:467-471; dead code in nbody-par), rendered by a CUDA kernel.
  */
 #include <errno.h>
 #include <stdio.h>
@@ -24,6 +25,7 @@
 #include <string.h>
 #include <math.h>
 #include <sys/time.h>
+#include <time.h>
 
 #include "nbody_gpu.h"
 
@@ -53,7 +55,7 @@ static int read_number(FILE *f, int *out)
 }
 
 /* Width and height from a binary PPM header: "P6" <w> <h> <maxval<=255> <one whitespace>. */
-static int read_p6_dims(const char *path, int *xdim, int *ydim)
+static int read_p6_dims(const char *path, int *xdim, int *ydim, long *data_offset)
 {
     FILE *f = fopen(path, "rb");
     int maxval = 0;
@@ -64,8 +66,34 @@ static int read_p6_dims(const char *path, int *xdim, int *ydim)
         fclose(f);
         return -1;
     }
+    {
+        int c = fgetc(f);   /* exactly one whitespace character, then the 24-bit data (nbody-seq.c:287-296) */
+        if (c != ' ' && c != '\t' && c != '\n' && c != '\r') { errno = EPROTO; fclose(f); return -1; }
+    }
+    *data_offset = ftell(f);
     fclose(f);
     return 0;
+}
+
+/* display() + msync of the reference (nbody-seq.c:467-471): paint the current state into the P6 file. */
+static void write_image(nbody_gpu *h, const char *path, long data_offset, int xdim, int ydim)
+{
+    size_t bytes = (size_t)xdim * ydim * 3;
+    unsigned char *img = malloc(bytes);
+    FILE *f;
+    if (!img) return;
+    if (nbody_gpu_render(h, img) != 0) {
+        fprintf(stderr, "nbody_gpu_render: %s\n", nbody_gpu_last_error());
+        exit(1);
+    }
+    f = fopen(path, "r+b");
+    if (f) {
+        if (fseek(f, data_offset, SEEK_SET) == 0) fwrite(img, 1, bytes, f);
+        fclose(f);
+    } else {
+        fprintf(stderr, "Cannot write %s: %s\n", path, strerror(errno));
+    }
+    free(img);
 }
 
 static long long nr_flops(long long n, long long steps)
@@ -89,7 +117,8 @@ static void die_gpu(const char *what)
 
 int main(int argc, char **argv)
 {
-    int run_xps = 0, measure_comm = 0, hex = 0;
+    int run_xps = 0, measure_comm = 0, hex = 0, display_final = 0;
+    long data_offset = 0;
 #ifdef NBODY_SEQ
     int ngpus = 1;
     const char *usage_flags = "[--run-xps]";
@@ -111,6 +140,7 @@ int main(int argc, char **argv)
         else if (strcmp(argv[i], "--measure-comm") == 0) measure_comm = 1;
         else if (strcmp(argv[i], "--openmp") == 0) { /* accepted: the GPU threads are the worksharing */ }
         else if (strcmp(argv[i], "--hex") == 0) hex = 1;
+        else if (strcmp(argv[i], "--display-final") == 0) display_final = 1;
         else if (strcmp(argv[i], "--gpus") == 0 && i + 1 < argc) ngpus = atoi(argv[++i]);
         else if (strcmp(argv[i], "--mode") == 0 && i + 1 < argc)
             mode = strcmp(argv[++i], "fast") == 0 ? NBODY_GPU_MODE_FAST : NBODY_GPU_MODE_EXACT;
@@ -124,10 +154,9 @@ int main(int argc, char **argv)
     }
     if (nb > 0x7fffffffL / 2) nb = 0x7fffffffL / 2;
     const int n = (int)nb;
-    const int secsup = atoi(argv[2]);   /* secs_per_update: parsed, unused (display() is dead in nbody-par) */
-    (void)secsup;
+    const int secsup = atoi(argv[2]);   /* secs_per_update > 0: paint the world into the PPM every secsup seconds */
     int xdim = 0, ydim = 0;
-    if (read_p6_dims(argv[3], &xdim, &ydim) == -1) {
+    if (read_p6_dims(argv[3], &xdim, &ydim, &data_offset) == -1) {
         fprintf(stderr, "Cannot read %s: %s\n", argv[3], strerror(errno));
         exit(1);
     }
@@ -177,12 +206,25 @@ int main(int argc, char **argv)
         float ms[4];
         if (nbody_gpu_step_profiled(h, steps, 0, ms) != 0) die_gpu("nbody_gpu_step_profiled");
         comm_overhead = ms[3] / 1000.0;
+    } else if (secsup > 0) {
+        /* nbody-seq.c:457-471: the step loop with the timed display; the clock is looked at every 16 steps */
+        long lastup = 0;
+        for (int done = 0; done < steps;) {
+            int chunk = steps - done < 16 ? steps - done : 16;
+            if (nbody_gpu_step(h, chunk) != 0) die_gpu("nbody_gpu_step");
+            done += chunk;
+            if ((long)time(0) - lastup > secsup) {
+                write_image(h, argv[3], data_offset, xdim, ydim);
+                lastup = (long)time(0);
+            }
+        }
     } else {
         if (nbody_gpu_step(h, steps) != 0) die_gpu("nbody_gpu_step");
     }
     if (nbody_gpu_sync(h) != 0) die_gpu("nbody_gpu_sync");
     const double rtime = now_seconds() - start;
 
+    if (display_final) write_image(h, argv[3], data_offset, xdim, ydim);
     if (nbody_gpu_fetch(h, x, y, xf, yf, xv, yv) != 0) die_gpu("nbody_gpu_fetch");
     const double gflops = nr_flops(n, steps) / 1e9 / rtime;
 

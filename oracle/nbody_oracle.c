@@ -241,6 +241,35 @@ int oracle_run(int n, int xdim, int ydim, int steps, int trig, int threads,
     return 0;
 }
 
+/* display(): nbody-seq.c:307-354.  For every pixel the first body whose disc (radius R+0.5) covers it
+ * gives the tint, else black.  image = xdim*ydim*3 bytes.  (The tint product is formed in 64-bit; the
+ * reference's int product is identical for bodyCt <= 524288.) */
+void oracle_display(int n, int xdim, int ydim, const double *x, const double *y, const double *radius,
+                    unsigned char *image)
+{
+    double i, j;
+    for (j = 0; j < ydim; ++j) {
+        for (i = 0; i < xdim; ++i) {
+            unsigned char *p = image + (3 * ((long)i + ((long)j * xdim)));
+            int b;
+            for (b = 0; b < n; ++b) {
+                double dy = y[b] - j;
+                double dx = x[b] - i;
+                double d = sqrt(dx*dx + dy*dy);
+                if (d <= radius[b] + 0.5) break;
+            }
+            if (b < n) {
+                int tint = (int)((0xfffLL * (b + 1)) / (n + 2));
+                p[0] = (tint & 0xf) << 4;
+                p[1] = (tint & 0xf0);
+                p[2] = (tint & 0xf00) >> 4;
+            } else {
+                p[2] = (p[1] = (p[0] = 0));
+            }
+        }
+    }
+}
+
 /* The reference's flop model, nbody-seq.c:367-380, in 64-bit. */
 long long oracle_nr_flops(long long n, long long steps)
 {

@@ -62,6 +62,7 @@ def lib():
     L.nbody_gpu_step_profiled.argtypes = [vp, ci, ci, ctypes.POINTER(ctypes.c_float)]
     L.nbody_gpu_forces.argtypes = [vp, _dp, _dp]
     L.nbody_gpu_fetch.argtypes = [vp] + [odp] * 6
+    L.nbody_gpu_render.argtypes = [vp, np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")]
     L.nbody_gpu_sync.argtypes = [vp]
     L.nbody_gpu_destroy.argtypes = [vp]
     L.nbody_gpu_destroy.restype = None
@@ -164,6 +165,12 @@ class NBodyGPU:
         out = [np.empty(self.n) for _ in range(6)]
         _check(lib().nbody_gpu_fetch(self._h, *[a.ctypes.data_as(ctypes.c_void_p) for a in out]))
         return tuple(out)
+
+    def render(self, xdim, ydim):
+        """The reference's display() of the current positions: uint8 image (ydim, xdim, 3)."""
+        img = np.zeros((ydim, xdim, 3), dtype=np.uint8)
+        _check(lib().nbody_gpu_render(self._h, img))
+        return img
 
     def sync(self):
         _check(lib().nbody_gpu_sync(self._h))

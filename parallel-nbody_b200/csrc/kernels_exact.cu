@@ -5,6 +5,7 @@
 
 #include "step_kernels.cuh"
 #include "forces_exact_wide.cuh"
+#include "render.cuh"
 
 namespace nbody {
 
@@ -28,6 +29,15 @@ void launch_integrate_exact(const IntegrateArgs &a, cudaStream_t st)
     const int rows = a.hi - a.lo;
     if (rows <= 0) return;
     integrate_kernel<MODE_EXACT><<<(rows + 127) / 128, 128, 0, st>>>(a);
+}
+
+void launch_render(const double2 *pos, const double2 *mr, int n, int xdim, int ydim, int *owner, unsigned char *rgb,
+                   cudaStream_t st)
+{
+    const int npix = xdim * ydim;
+    render_clear_kernel<<<(npix + 255) / 256, 256, 0, st>>>(owner, npix);
+    render_cover_kernel<<<n, 128, 0, st>>>(pos, mr, n, xdim, ydim, owner);
+    render_paint_kernel<<<(npix + 255) / 256, 256, 0, st>>>(owner, npix, n, rgb);
 }
 
 }  // namespace nbody

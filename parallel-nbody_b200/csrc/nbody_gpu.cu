@@ -791,6 +791,26 @@ int nbody_gpu_describe(const nbody_gpu *h, char *buf, int len)
     return need + 1;
 }
 
+int nbody_gpu_render(nbody_gpu *h, unsigned char *rgb)
+{
+    if (!h || !rgb) return fail(NBODY_GPU_EINVAL, "NULL argument");
+    Shard &s = h->shards[0];   // every device holds all current positions
+    NB_CUDA(cudaSetDevice(s.device));
+    const size_t npix = static_cast<size_t>(h->cfg.xdim) * h->cfg.ydim;
+    int *owner = nullptr;
+    unsigned char *img = nullptr;
+    NB_CUDA(cudaMalloc(&owner, npix * sizeof(int)));
+    NB_CUDA(cudaMalloc(&img, npix * 3));
+    launch_render(s.pos[h->cur], s.mr, h->n, h->cfg.xdim, h->cfg.ydim, owner, img, s.stream);
+    h->launches[2] += 3;
+    cudaError_t e = cudaMemcpyAsync(rgb, img, npix * 3, cudaMemcpyDeviceToHost, s.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
+    cudaFree(owner);
+    cudaFree(img);
+    if (e != cudaSuccess) return fail(NBODY_GPU_ECUDA, "render failed: %s", cudaGetErrorString(e));
+    return NBODY_GPU_OK;
+}
+
 long long nbody_gpu_launch_count(const nbody_gpu *h, long long out[4])
 {
     if (!h) return 0;

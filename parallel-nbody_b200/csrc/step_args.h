@@ -92,6 +92,8 @@ void launch_forces_fast(const ForceArgs &a, int nsplit, cudaStream_t st);
 void launch_integrate_fast(const IntegrateArgs &a, cudaStream_t st);
 void launch_reduce_fast(const IntegrateArgs &a, cudaStream_t st);
 int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream_t st);   // returns cudaError_t
+void launch_render(const double2 *pos, const double2 *mr, int n, int xdim, int ydim, int *owner, unsigned char *rgb,
+                   cudaStream_t st);
 void launch_sym_reduce(const SymReduceArgs &a, cudaStream_t st);
 
 }  // namespace nbody

@@ -37,6 +37,8 @@ def lib():
     L.oracle_positions.argtypes = [i, i, i] + [_dp] * 6
     L.oracle_run.argtypes = [i, i, i, i, i, i] + [_dp] * 8
     L.oracle_run.restype = i
+    L.oracle_display.argtypes = [i, i, i, _dp, _dp, _dp, np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")]
+    L.oracle_display.restype = None
     L.oracle_nr_flops.argtypes = [ctypes.c_longlong, ctypes.c_longlong]
     L.oracle_nr_flops.restype = ctypes.c_longlong
     for f in ("oracle_det_atan2_v", "oracle_libm_atan2_v", "oracle_det_sincos_v", "oracle_libm_sincos_v"):
@@ -74,6 +76,13 @@ def run(b, steps, trig, xdim=1024, ydim=768, threads=1):
                           b.x, b.y, b.xf, b.yf, b.xv, b.yv, b.mass, b.radius)
     assert rc == 0
     return b
+
+
+def display(b, xdim=1024, ydim=768):
+    """The reference's display() on the CPU: uint8 image (ydim, xdim, 3)."""
+    img = np.zeros((ydim, xdim, 3), dtype=np.uint8)
+    lib().oracle_display(b.n, xdim, ydim, b.x, b.y, b.radius, img)
+    return img
 
 
 def format_state(x, y, xf, yf, xv, yv):

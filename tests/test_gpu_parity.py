@@ -245,3 +245,17 @@ def test_large_n_exact_sampled_rows(nb, oracle):
         sl = slice(lo, lo + 16)
         assert np.array_equal(gx[sl].view(np.uint64), xf[sl].view(np.uint64))
         assert np.array_equal(gy[sl].view(np.uint64), yf[sl].view(np.uint64))
+
+
+@pytest.mark.parametrize("n,steps", [(128, 200), (32, 0), (3000, 3)])
+def test_render_matches_reference_display(nb, oracle, n, steps):
+    """display() (nbody-seq.c:326-354) as a CUDA rasteriser: byte-identical to the CPU restatement."""
+    xdim, ydim = (1024, 768) if n < 1000 else (320, 200)
+    b = oracle.init_bodies(n, xdim, ydim)
+    g = nb.NBodyGPU(b.x, b.y, b.xv, b.yv, b.mass, b.radius, xdim=xdim, ydim=ydim, mode=nb.MODE_EXACT)
+    g.step(steps)
+    img = g.render(xdim, ydim)
+    oracle.run(b, steps, trig=1, xdim=xdim, ydim=ydim)
+    ref = oracle.display(b, xdim, ydim)
+    assert img.shape == ref.shape and np.array_equal(img, ref)
+    assert ref.any()     # something was painted

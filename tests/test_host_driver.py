@@ -130,3 +130,22 @@ def test_strict_runner(workdir, oracle):
                        cwd=workdir, env=_env(), capture_output=True, text=True)
     assert r.returncode == 0, r.stdout
     assert r.stdout.count("STATUS=PASSED") == 25 and "FAILED" not in r.stdout
+
+
+@pytest.mark.gpu
+def test_driver_display_final_writes_ppm(workdir, oracle):
+    """secs_per_update / --display-final: the CUDA rasteriser's image lands behind the P6 header."""
+    ppm2 = str(workdir / "img.ppm")
+    oracle.write_ppm(ppm2, 256, 192)
+    r = subprocess.run(["nbody/nbody-par", "64", "0", "img.ppm", "50", "--display-final"], cwd=workdir,
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    data = open(ppm2, "rb").read()
+    hdr = b"P6\n256 192\n255\n"
+    assert data.startswith(hdr) and len(data) == len(hdr) + 256 * 192 * 3
+    img = np.frombuffer(data[len(hdr):], dtype=np.uint8).reshape(192, 256, 3)
+    b = oracle.init_bodies(64, 256, 192)
+    oracle.run(b, 50, trig=1, xdim=256, ydim=192)
+    assert np.array_equal(img, oracle.display(b, 256, 192))
+    r = subprocess.run(["nbody/nbody-seq", "64", "1", "img.ppm", "40"], cwd=workdir, capture_output=True, text=True)
+    assert r.returncode == 0 and open(ppm2, "rb").read().startswith(hdr)
