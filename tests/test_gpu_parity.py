@@ -259,3 +259,44 @@ def test_render_matches_reference_display(nb, oracle, n, steps):
     ref = oracle.display(b, xdim, ydim)
     assert img.shape == ref.shape and np.array_equal(img, ref)
     assert ref.any()     # something was painted
+
+
+def _rel(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+@pytest.mark.parametrize("n,steps", [(65536, 200), (262144, 50)])
+def test_baseline_configs_3_and_4_full_size_properties(nb, oracle, n, steps):
+    """BASELINE configs 3 (N=65536 x 200 steps) and 4 (N=262144 x 50 steps), fast mode, at FULL size.  The CPU
+    oracle would need hours here, so the checks are size-independent: (1) the symmetric kernel (each pair
+    once, reactions reduced across lanes/warps/blocks) and the directed kernel (every body sums its own row)
+    are two independent summation structures of the same physics and must agree after the whole run to far
+    better than the stated tolerance; (2) run-to-run bit determinism; (3) bodies stay inside the world;
+    (4) the last step's pair forces obey Newton's third law (sum ~ 0 against sum |F|); (5) a sample of rows of
+    the FINAL state's forces is recomputed by the CPU oracle from the final positions."""
+    b = oracle.init_bodies(n)
+    gs = make(nb, b, mode=nb.MODE_FAST, symmetric=1)
+    gd = make(nb, b, mode=nb.MODE_FAST, symmetric=-1)
+    gs.step(steps)
+    gd.step(steps)
+    s = gs.fetch()
+    d = gd.fetch()
+    assert _rel(s[0], d[0]) <= 1e-12 and _rel(s[1], d[1]) <= 1e-12          # positions
+    assert _rel(s[4], d[4]) <= 1e-10 and _rel(s[5], d[5]) <= 1e-10          # velocities
+    fscale = max(np.abs(d[2]).max(), np.abs(d[3]).max())
+    assert np.abs(s[2] - d[2]).max() <= 1e-8 * fscale and np.abs(s[3] - d[3]).max() <= 1e-8 * fscale
+    g2 = make(nb, b, mode=nb.MODE_FAST, symmetric=1)
+    g2.step(steps)
+    for a, c in zip(s, g2.fetch()):
+        assert np.array_equal(a.view(np.uint64), c.view(np.uint64))
+    assert s[0].min() >= 0 and s[0].max() < 1024 and s[1].min() >= 0 and s[1].max() < 768
+    assert abs(s[2].sum()) <= 1e-9 * np.abs(s[2]).sum() and abs(s[3].sum()) <= 1e-9 * np.abs(s[3]).sum()
+    # forces at the final positions (the state after the last step), sampled rows vs the CPU oracle
+    fx, fy = gs.forces()
+    xf, yf = np.zeros(n), np.zeros(n)
+    rows = 8
+    for lo in (0, n // 2 + 3, n - rows):
+        oracle.lib().oracle_forces_rows(n, 0, lo, lo + rows, 8, s[0], s[1], b.mass, b.radius, xf, yf)
+        sl = slice(lo, lo + rows)
+        sc = max(np.abs(xf[sl]).max(), np.abs(yf[sl]).max())
+        assert np.abs(fx[sl] - xf[sl]).max() <= 1e-10 * sc and np.abs(fy[sl] - yf[sl]).max() <= 1e-10 * sc
