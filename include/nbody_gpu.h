@@ -65,6 +65,8 @@ typedef struct nbody_gpu_cfg {
     int use_graph;  /* 1 = capture the step loop in a CUDA graph (default when 0: yes), -1 = plain launches */
     int symmetric;  /* fast mode: 1 = evaluate each unordered pair once (+f to i, -f to j, like nbody-seq.c:103-106),
                        -1 = directed evaluation only, 0 = library default (symmetric on one GPU for n >= 8192) */
+    int p2p;        /* sharded symmetric fast mode: 0 = fuse the per-step exchange into the kernels over NVLink peer
+                       memory when the GPUs can map each other (else ncclAllGather), 1 = require it, -1 = NCCL only */
 } nbody_gpu_cfg;
 
 /* Replaces calloc(world) + initialize_simulation_data + MPI_Bcast

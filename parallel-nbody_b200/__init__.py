@@ -32,7 +32,7 @@ class _Cfg(ctypes.Structure):
     _fields_ = [("n", ctypes.c_int), ("xdim", ctypes.c_int), ("ydim", ctypes.c_int),
                 ("mode", ctypes.c_int), ("ngpus", ctypes.c_int), ("device", ctypes.c_int),
                 ("rank", ctypes.c_int), ("nranks", ctypes.c_int), ("nccl_id", ctypes.c_void_p),
-                ("jsplit", ctypes.c_int), ("use_graph", ctypes.c_int), ("symmetric", ctypes.c_int)]
+                ("jsplit", ctypes.c_int), ("use_graph", ctypes.c_int), ("symmetric", ctypes.c_int), ("p2p", ctypes.c_int)]
 
 
 _lib = None
@@ -125,7 +125,7 @@ class NBodyGPU:
     """One N-body world on the GPU(s). Arrays are host numpy float64 of length n."""
 
     def __init__(self, x, y, xv, yv, mass, radius, xdim=1024, ydim=768, mode=MODE_EXACT,
-                 ngpus=1, device=-1, rank=0, nranks=1, nccl_id=None, jsplit=0, use_graph=0, symmetric=0):
+                 ngpus=1, device=-1, rank=0, nranks=1, nccl_id=None, jsplit=0, use_graph=0, symmetric=0, p2p=0):
         x, y, xv, yv, mass, radius = map(_f64, (x, y, xv, yv, mass, radius))
         self.n = int(x.shape[0])
         for a in (y, xv, yv, mass, radius):
@@ -133,7 +133,7 @@ class NBodyGPU:
                 raise ValueError("all body arrays must have the same length")
         self._id = ctypes.create_string_buffer(nccl_id, NCCL_ID_BYTES) if nccl_id else None
         cfg = _Cfg(self.n, xdim, ydim, mode, ngpus, device, rank, nranks,
-                   ctypes.cast(self._id, ctypes.c_void_p) if self._id else None, jsplit, use_graph, symmetric)
+                   ctypes.cast(self._id, ctypes.c_void_p) if self._id else None, jsplit, use_graph, symmetric, p2p)
         self._h = ctypes.c_void_p()
         _check(lib().nbody_gpu_init(ctypes.byref(self._h), ctypes.byref(cfg), x, y, xv, yv, mass, radius))
 

@@ -4,6 +4,7 @@
 #include "step_kernels.cuh"
 #include "forces_fast.cuh"
 #include "forces_sym.cuh"
+#include "p2p.cuh"
 
 namespace nbody {
 
@@ -71,6 +72,23 @@ void launch_sym_reduce(const SymReduceArgs &a, cudaStream_t st)
     if (a.n <= 0 || a.nv <= 0) return;
     dim3 grid((a.n + 127) / 128, a.nv);
     sym_reduce_kernel<<<grid, 128, 0, st>>>(a);
+}
+
+void launch_sym_reduce_p2p(const SymReduceArgs &a, const PeerTable &t, int rows_per_shard, cudaStream_t st)
+{
+    if (a.n <= 0 || a.nv <= 0) return;
+    dim3 grid((a.n + 127) / 128, a.nv);
+    sym_reduce_p2p_kernel<<<grid, 128, 0, st>>>(a, t, rows_per_shard);
+}
+
+void launch_p2p_signal(const PeerTable &t, int phase, unsigned long long epoch, cudaStream_t st)
+{
+    p2p_signal_kernel<<<1, 32, 0, st>>>(t, phase, epoch);
+}
+
+void launch_p2p_wait(const PeerTable &t, int phase, unsigned long long epoch, int *error_word, cudaStream_t st)
+{
+    p2p_wait_kernel<<<1, 32, 0, st>>>(t, phase, epoch, error_word);
 }
 
 void launch_reduce_fast(const IntegrateArgs &a, cudaStream_t st)

@@ -61,6 +61,10 @@ struct Shard {
     double2 *colpart = nullptr;  // symmetric fast kernel: reaction partial sums [owned blocks][npad]
     double2 *vbuf = nullptr;     // symmetric fast kernel: per-virtual-rank force vectors [SYM_V][npad]
     int v0 = 0, nv = SYM_V;      // virtual ranks owned by this shard
+    PeerTable peers = {};        // fused peer-memory exchange (npeers = 0: not in use)
+    unsigned long long *flags = nullptr;   // [2][MAX_PEERS] epoch words written by the peers
+    int *p2p_err = nullptr;      // set by a wait kernel that timed out
+    std::vector<void *> ipc_opened;
     int nblocks_owned = 0;       // colpart slots (row blocks of the owned virtual ranks, whole groups)
     NcclComm comm = nullptr;
     cudaGraphExec_t graph[2] = {nullptr, nullptr};   // indexed by the starting slot
@@ -79,6 +83,8 @@ struct nbody_gpu {
     int nsplit = 1;              // fast mode: j-chunks
     int chunk = 0;               // fast mode: j-chunk length
     bool symmetric = false;      // fast mode: evaluate each unordered pair once (forces_sym_kernel)
+    bool p2p = false;            // sharded symmetric: exchange fused into the kernels over peer memory (no NCCL per step)
+    unsigned long long epoch = 0;
     int nblocks = 0;             // symmetric: number of SYM_RB row blocks
     int cur = 0;                 // slot holding the current positions (the reference's world->old)
     int graph_steps = 0;         // steps captured per graph launch (even), 0 = graphs off
@@ -145,7 +151,11 @@ static void free_shard(Shard &s)
     if (s.frc) cudaFree(s.frc);
     if (s.part) cudaFree(s.part);
     if (s.colpart) cudaFree(s.colpart);
+    for (void *m : s.ipc_opened) cudaIpcCloseMemHandle(m);
+    s.ipc_opened.clear();
     if (s.vbuf) cudaFree(s.vbuf);
+    if (s.flags) cudaFree(s.flags);
+    if (s.p2p_err) cudaFree(s.p2p_err);
     if (s.ev0) cudaEventDestroy(s.ev0);
     if (s.ev1) cudaEventDestroy(s.ev1);
     if (s.comm) {
@@ -186,10 +196,18 @@ static IntegrateArgs integrate_args(const nbody_gpu *h, const Shard &s, int slot
     a.npad = h->npad;
     // symmetric kernel: every device holds the complete force vectors after the exchange and integrates
     // ALL bodies (identical bits everywhere), which saves the position all-gather
-    a.lo = h->symmetric ? 0 : s.lo;
-    a.hi = h->symmetric ? h->n : s.hi;
+    // (with the fused peer exchange each device integrates its own rows and stores the new positions to all)
+    const bool all_rows = h->symmetric && !h->p2p;
+    a.lo = all_rows ? 0 : s.lo;
+    a.hi = all_rows ? h->n : s.hi;
     a.xdim = h->cfg.xdim;
     a.ydim = h->cfg.ydim;
+    a.npeers = 0;
+    for (int r = 0; r < MAX_PEERS; ++r) a.peer_pos_new[r] = nullptr;
+    if (h->p2p) {
+        a.npeers = s.peers.npeers;
+        for (int r = 0; r < s.peers.npeers; ++r) a.peer_pos_new[r] = s.peers.pos[slot ^ 1][r];
+    }
     return a;
 }
 
@@ -216,7 +234,7 @@ static void enqueue_forces(nbody_gpu *h, Shard &s, int slot)
     }
 }
 
-static void enqueue_sym_reduce(nbody_gpu *h, Shard &s)
+static void enqueue_sym_reduce(nbody_gpu *h, Shard &s, bool to_peers = false)
 {
     SymReduceArgs a;
     a.rowpart = s.part;
@@ -228,7 +246,8 @@ static void enqueue_sym_reduce(nbody_gpu *h, Shard &s)
     a.nsplit = h->nsplit;
     a.v0 = s.v0;
     a.nv = s.nv;
-    launch_sym_reduce(a, s.stream);
+    if (to_peers) launch_sym_reduce_p2p(a, s.peers, h->rows_per_shard, s.stream);
+    else launch_sym_reduce(a, s.stream);
 }
 
 static void enqueue_integrate(nbody_gpu *h, Shard &s, int slot)
@@ -279,8 +298,9 @@ struct StepMarks {
 };
 
 // One step on every local shard, reading slot h->cur:
-//   forces [+ symmetric fold] | (symmetric & sharded: all-gather of the virtual-rank vectors)
-//   | integrate | (directed & sharded: all-gather of the new positions) | flip.
+//   forces [+ symmetric fold] | exchange A (symmetric & sharded: the virtual-rank force vectors)
+//   | integrate | exchange B (the new positions) | flip.
+// Exchanges: fused peer-memory stores + signal/wait kernels (h->p2p), else ncclAllGather.
 // Phases for marks: 0 start, 1 after forces, 2 after fold, 3 after exchange A, 4 after integrate, 5 after exchange B.
 static int run_one_step(nbody_gpu *h, StepMarks *marks)
 {
@@ -293,6 +313,7 @@ static int run_one_step(nbody_gpu *h, StepMarks *marks)
         }                                                       \
     }
     NB_MARK(0)
+    h->epoch += 1;
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
         enqueue_forces(h, s, h->cur);
@@ -302,12 +323,19 @@ static int run_one_step(nbody_gpu *h, StepMarks *marks)
     if (h->symmetric) {
         for (Shard &s : h->shards) {
             NB_CUDA(cudaSetDevice(s.device));
-            enqueue_sym_reduce(h, s);
+            enqueue_sym_reduce(h, s, h->p2p);
+            if (h->p2p) launch_p2p_signal(s.peers, 0, h->epoch, s.stream);
         }
-        h->launches[2] += static_cast<long long>(nsh);
+        h->launches[2] += static_cast<long long>(nsh) * (h->p2p ? 2 : 1);
     }
     NB_MARK(2)
-    if (h->symmetric) {
+    if (h->p2p) {
+        for (Shard &s : h->shards) {
+            NB_CUDA(cudaSetDevice(s.device));
+            launch_p2p_wait(s.peers, 0, h->epoch, s.p2p_err, s.stream);
+        }
+        h->launches[2] += static_cast<long long>(nsh);
+    } else if (h->symmetric) {
         int rc = allgather(h, AG_VBUF);
         if (rc) return rc;
     }
@@ -315,10 +343,17 @@ static int run_one_step(nbody_gpu *h, StepMarks *marks)
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
         enqueue_integrate(h, s, h->cur);
+        if (h->p2p) launch_p2p_signal(s.peers, 1, h->epoch, s.stream);
     }
     h->launches[1] += static_cast<long long>(nsh);
     NB_MARK(4)
-    if (!h->symmetric) {
+    if (h->p2p) {
+        for (Shard &s : h->shards) {
+            NB_CUDA(cudaSetDevice(s.device));
+            launch_p2p_wait(s.peers, 1, h->epoch, s.p2p_err, s.stream);
+        }
+        h->launches[2] += static_cast<long long>(nsh) * 2;
+    } else if (!h->symmetric) {
         int rc = allgather(h, h->cur ^ 1);
         if (rc) return rc;
     }
@@ -366,6 +401,11 @@ static int sync_all(nbody_gpu *h)
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
         NB_CUDA(cudaStreamSynchronize(s.stream));
+        if (h->p2p && s.p2p_err) {
+            int e = 0;
+            NB_CUDA(cudaMemcpy(&e, s.p2p_err, sizeof e, cudaMemcpyDeviceToHost));
+            if (e) return fail(NBODY_GPU_ECUDA, "peer exchange %c timed out waiting for another GPU", e == 1 ? 'A' : 'B');
+        }
     }
     return NBODY_GPU_OK;
 }
@@ -397,6 +437,119 @@ static int do_steps(nbody_gpu *h, int steps)
         NB_CUDA(cudaSetDevice(s.device));
         NB_CUDA(cudaGetLastError());
     }
+    return NBODY_GPU_OK;
+}
+
+
+// Build the peer-memory tables for the fused exchange.  Single process: cudaDeviceEnablePeerAccess between
+// all local devices.  One process per GPU: CUDA IPC handles of vbuf / pos[0] / pos[1] / flags, all-gathered
+// through the NCCL communicator that already exists for the bootstrap.  Returns NBODY_GPU_OK with
+// h->p2p = false when peer access is not possible (the NCCL path is then used).
+static int setup_p2p(nbody_gpu *h)
+{
+    const int P = h->nshards_total;
+    if (P > MAX_PEERS) return NBODY_GPU_OK;
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        NB_CUDA(cudaMalloc(&s.flags, sizeof(unsigned long long) * 2 * MAX_PEERS));
+        NB_CUDA(cudaMemset(s.flags, 0, sizeof(unsigned long long) * 2 * MAX_PEERS));
+        NB_CUDA(cudaMalloc(&s.p2p_err, sizeof(int)));
+        NB_CUDA(cudaMemset(s.p2p_err, 0, sizeof(int)));
+    }
+    if (h->shards.size() > 1) {   // one process, several devices
+        for (Shard &a : h->shards) {
+            for (Shard &b : h->shards) {
+                if (a.device == b.device) continue;
+                int ok = 0;
+                NB_CUDA(cudaDeviceCanAccessPeer(&ok, a.device, b.device));
+                if (!ok) return NBODY_GPU_OK;
+                NB_CUDA(cudaSetDevice(a.device));
+                cudaError_t e = cudaDeviceEnablePeerAccess(b.device, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return NBODY_GPU_OK;
+                cudaGetLastError();
+            }
+        }
+        for (Shard &a : h->shards) {
+            a.peers.npeers = P;
+            a.peers.me = a.part_index;
+            for (Shard &b : h->shards) {
+                a.peers.vbuf[b.part_index] = b.vbuf;
+                a.peers.pos[0][b.part_index] = b.pos[0];
+                a.peers.pos[1][b.part_index] = b.pos[1];
+                a.peers.flags[b.part_index] = b.flags;
+            }
+        }
+        h->p2p = true;
+        return NBODY_GPU_OK;
+    }
+    // one process per GPU
+    Shard &s = h->shards[0];
+    const NcclApi *api = nccl_api(nullptr);
+    if (!api) return NBODY_GPU_OK;
+    struct Handles { cudaIpcMemHandle_t m[4]; };
+    static_assert(sizeof(Handles) % sizeof(double) == 0, "handles travel as doubles");
+    Handles mine;
+    void *ptrs[4] = {s.vbuf, s.pos[0], s.pos[1], s.flags};
+    NB_CUDA(cudaSetDevice(s.device));
+    int ipc_ok = 1;
+    for (int k = 0; k < 4; ++k) {
+        if (cudaIpcGetMemHandle(&mine.m[k], ptrs[k]) != cudaSuccess) {
+            cudaGetLastError();
+            ipc_ok = 0;
+            memset(&mine.m[k], 0, sizeof mine.m[k]);
+        }
+    }
+    // every rank must take the same decision: gather the handles plus an "ok" marker
+    struct Packet { Handles h; double ok; };
+    Packet *dev = nullptr;
+    std::vector<Packet> all(P);
+    NB_CUDA(cudaMalloc(&dev, sizeof(Packet) * P));
+    Packet pk;
+    pk.h = mine;
+    pk.ok = ipc_ok;
+    NB_CUDA(cudaMemcpyAsync(dev + s.part_index, &pk, sizeof pk, cudaMemcpyHostToDevice, s.stream));
+    NB_NCCL(api, api->AllGather(dev + s.part_index, dev, sizeof(Packet) / sizeof(double), NCCL_DOUBLE, s.comm, s.stream));
+    NB_CUDA(cudaMemcpyAsync(all.data(), dev, sizeof(Packet) * P, cudaMemcpyDeviceToHost, s.stream));
+    NB_CUDA(cudaStreamSynchronize(s.stream));
+    cudaFree(dev);
+    for (int r = 0; r < P; ++r)
+        if (all[r].ok != 1.0) return NBODY_GPU_OK;
+    s.peers.npeers = P;
+    s.peers.me = s.part_index;
+    int opened_all = 1;
+    for (int r = 0; r < P; ++r) {
+        void *q[4];
+        if (r == s.part_index) {
+            for (int k = 0; k < 4; ++k) q[k] = ptrs[k];
+        } else {
+            for (int k = 0; k < 4; ++k) {
+                q[k] = nullptr;
+                if (cudaIpcOpenMemHandle(&q[k], all[r].h.m[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                    cudaGetLastError();
+                    opened_all = 0;
+                } else {
+                    s.ipc_opened.push_back(q[k]);
+                }
+            }
+        }
+        s.peers.vbuf[r] = static_cast<double2 *>(q[0]);
+        s.peers.pos[0][r] = static_cast<double2 *>(q[1]);
+        s.peers.pos[1][r] = static_cast<double2 *>(q[2]);
+        s.peers.flags[r] = static_cast<unsigned long long *>(q[3]);
+    }
+    // agree on the outcome (a rank that could not map a peer must not leave the others waiting for it)
+    double *flag = nullptr;
+    std::vector<double> oks(P);
+    NB_CUDA(cudaMalloc(&flag, sizeof(double) * P));
+    const double my = opened_all;
+    NB_CUDA(cudaMemcpyAsync(flag + s.part_index, &my, sizeof my, cudaMemcpyHostToDevice, s.stream));
+    NB_NCCL(api, api->AllGather(flag + s.part_index, flag, 1, NCCL_DOUBLE, s.comm, s.stream));
+    NB_CUDA(cudaMemcpyAsync(oks.data(), flag, sizeof(double) * P, cudaMemcpyDeviceToHost, s.stream));
+    NB_CUDA(cudaStreamSynchronize(s.stream));
+    cudaFree(flag);
+    for (int r = 0; r < P; ++r)
+        if (oks[r] != 1.0) return NBODY_GPU_OK;
+    h->p2p = true;
     return NBODY_GPU_OK;
 }
 
@@ -546,8 +699,11 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
     int rc = upload(h, nullptr, 0, x, y);
     if (!rc) rc = upload(h, &Shard::mr, 0, mass, radius);
     if (!rc) rc = upload(h, &Shard::vel, 0, xv, yv);
-    // padding rows of mr must not be zero-radius/zero-mass hazards: they are never read (j < n)
     h->cur = 0;
+    if (!rc && h->sharded && h->symmetric && cfg->p2p >= 0) {
+        rc = setup_p2p(h);
+        if (!rc && !h->p2p && cfg->p2p > 0) rc = fail(NBODY_GPU_ECUDA, "peer-memory exchange requested but peer access is unavailable");
+    }
     return rc;
 }
 
@@ -735,7 +891,7 @@ int nbody_gpu_forces(nbody_gpu *h, double *xf, double *yf)
             h->launches[2] += 1;
         }
     }
-    if (!h->symmetric) rc = allgather(h, AG_FRC);
+    if (!h->symmetric || h->p2p) rc = allgather(h, AG_FRC);
     if (rc) return rc;
     Shard &s0 = h->shards[0];
     NB_CUDA(cudaSetDevice(s0.device));
@@ -748,7 +904,7 @@ int nbody_gpu_fetch(nbody_gpu *h, double *x, double *y, double *xf, double *yf, 
 {
     if (!h) return fail(NBODY_GPU_EINVAL, "handle is NULL");
     int rc = NBODY_GPU_OK;
-    if (h->sharded && !h->symmetric) {
+    if (h->sharded && (!h->symmetric || h->p2p)) {
         // forces and velocities live sharded during the run; gather them like the reference's
         // whole-struct MPI_Allgatherv leaves them (nbody-par.c:933-936)
         if (xv || yv) rc = allgather(h, AG_VEL);
@@ -781,9 +937,10 @@ int nbody_gpu_describe(const nbody_gpu *h, char *buf, int len)
     char tmp[512];
     const int need = snprintf(tmp, sizeof tmp,
                               "{\"mode\": \"%s\", \"kernel\": \"%s\", \"symmetric\": %s, \"nsplit\": %d, \"chunk\": %d, "
-                              "\"row_blocks\": %d, \"shards\": %d, \"graph_steps\": %d, \"fp64_instr_per_pair\": %.1f}",
+                              "\"row_blocks\": %d, \"shards\": %d, \"graph_steps\": %d, \"exchange\": \"%s\", \"fp64_instr_per_pair\": %.1f}",
                               fast ? "fast" : "exact", kernel, h->symmetric ? "true" : "false", h->nsplit, h->chunk,
-                              h->symmetric ? h->nblocks : 0, h->nshards_total, h->sharded ? 0 : h->graph_steps, ipp);
+                              h->symmetric ? h->nblocks : 0, h->nshards_total, h->sharded ? 0 : h->graph_steps,
+                              !h->sharded ? "none" : h->p2p ? "peer-memory stores + signal/wait kernels" : "ncclAllGather", ipp);
     if (buf && len > 0) {
         strncpy(buf, tmp, static_cast<size_t>(len) - 1);
         buf[len - 1] = 0;

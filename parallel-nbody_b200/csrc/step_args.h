@@ -71,6 +71,17 @@ struct SymReduceArgs {
     int v0, nv;
 };
 
+// Peer-memory view of a sharded job (all pointers are device addresses valid on THIS device: own memory,
+// cudaDeviceEnablePeerAccess mappings, or cudaIpcOpenMemHandle mappings).
+constexpr int MAX_PEERS = 8;
+struct PeerTable {
+    double2 *vbuf[MAX_PEERS];
+    double2 *pos[2][MAX_PEERS];
+    unsigned long long *flags[MAX_PEERS];   // [2 phases][MAX_PEERS sources] epoch words on each device
+    int npeers;                             // 0 = no peer exchange
+    int me;
+};
+
 struct IntegrateArgs {
     const double2 *pos_old;
     double2 *pos_new;
@@ -83,6 +94,8 @@ struct IntegrateArgs {
     int npad;
     int lo, hi;
     int xdim, ydim;
+    double2 *peer_pos_new[MAX_PEERS];   // fused position exchange: also store pos_new[i] here (npeers entries)
+    int npeers;                         // 0 = store to pos_new only
 };
 
 // launchers, defined in kernels_exact.cu / kernels_fast.cu
@@ -95,5 +108,8 @@ int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream
 void launch_render(const double2 *pos, const double2 *mr, int n, int xdim, int ydim, int *owner, unsigned char *rgb,
                    cudaStream_t st);
 void launch_sym_reduce(const SymReduceArgs &a, cudaStream_t st);
+void launch_sym_reduce_p2p(const SymReduceArgs &a, const PeerTable &t, int rows_per_shard, cudaStream_t st);
+void launch_p2p_signal(const PeerTable &t, int phase, unsigned long long epoch, cudaStream_t st);
+void launch_p2p_wait(const PeerTable &t, int phase, unsigned long long epoch, int *error_word, cudaStream_t st);
 
 }  // namespace nbody

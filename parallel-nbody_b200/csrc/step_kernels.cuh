@@ -240,7 +240,12 @@ __device__ __forceinline__ void integrate_body(const IntegrateArgs &a, int i, do
         v.y = -v.y;
     }
     a.vel[i] = v;
-    a.pos_new[i] = make_double2(xn, yn);
+    const double2 pn = make_double2(xn, yn);
+    if (a.npeers > 0) {
+        for (int r = 0; r < a.npeers; ++r) a.peer_pos_new[r][i] = pn;   // every GPU's copy, over NVLink (incl. our own)
+    } else {
+        a.pos_new[i] = pn;
+    }
 }
 
 // FAST: total force on body i from the partial sums, in a fixed order.  Directed kernel: the j-chunk

@@ -39,10 +39,13 @@ def test_symmetric_kernel_same_bits_on_1_2_4_8_gpus(nb, oracle, n, steps):
         pytest.skip("needs >= 2 GPUs")
     b = oracle.init_bodies(n)
     b.x[n - 1], b.y[n - 1] = b.x[1], b.y[1]          # a coincident pair across row blocks
-    def run(p):
-        g = nb.NBodyGPU(b.x, b.y, b.xv, b.yv, b.mass, b.radius, mode=1, ngpus=p, symmetric=1)
+    def run(p, p2p=0):
+        g = nb.NBodyGPU(b.x, b.y, b.xv, b.yv, b.mass, b.radius, mode=1, ngpus=p, symmetric=1, p2p=p2p)
         g.step(steps)
         out = g.fetch()
+        if p > 1:
+            want = "ncclAllGather" if p2p < 0 else "peer-memory"
+            assert want in g.describe()["exchange"], g.describe()
         g.close()
         return out
     ref = run(1)
@@ -53,9 +56,10 @@ def test_symmetric_kernel_same_bits_on_1_2_4_8_gpus(nb, oracle, n, steps):
     for p in (2, 4, 8):
         if p > k:
             continue
-        got = run(p)
-        for a, c in zip(ref, got):
-            assert np.array_equal(a.view(np.uint64), c.view(np.uint64)), (n, p)
+        for p2p in (1, -1):   # fused peer-memory exchange, and the NCCL all-gather path
+            got = run(p, p2p)
+            for a, c in zip(ref, got):
+                assert np.array_equal(a.view(np.uint64), c.view(np.uint64)), (n, p, p2p)
 
 
 def test_sharded_exact_matches_oracle_and_golden(nb, oracle):
