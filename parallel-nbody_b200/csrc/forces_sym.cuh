@@ -27,20 +27,40 @@ struct SymBody {
     int minhi;
 };
 
+// MUFU.RSQ64H reads and writes high words only; PTX's rsqrt.approx.f64 also zeroes the low word, which costs a
+// move per pair.  The seed is only good to 2^-22.9, so any low word will do: take it from a value that dies
+// here (the register pair is reused in place, no move).
+__device__ __forceinline__ double rsqrt_seed_donor(double q, double donor)
+{
+    int hi;
+    asm("{\n.reg .f64 t;\n.reg .b32 lo;\nrsqrt.approx.ftz.f64 t, %1;\nmov.b64 {lo, %0}, t;\n}" : "=r"(hi) : "d"(q));
+    return __hiloint2double(hi, __double2loint(donor));
+}
+
 // One unordered pair (i < j): row side into b.ax/ay, reaction side into (rx, ry).
+// FLAVOR bit 0: seed low word from a dead value; bit 1: one coincidence word per thread (min3); bit 2: far field
+// (no clamp, no coincidence test: the caller guarantees dsqr >= mindsqr > 0).
+template <int FLAVOR>
 __device__ __forceinline__ void pair_sym(SymBody &b, double xj, double yj, double mj, double rj, double &rx,
-                                         double &ry)
+                                         double &ry, int &minhi)
 {
     const double dx = xj - b.x;
     const double dy = yj - b.y;
     const double dsqr = fma(dx, dx, dy * dy);
-    const double mindist = b.r + rj;
-    const double mindsqr = mindist * mindist;
-    const double forced = __longlong_as_double(max(__double_as_longlong(dsqr), __double_as_longlong(mindsqr)));
-    b.minhi = min(b.minhi, __double2hiint(dsqr));
-    const double f2 = forced * forced;
-    const double q = fma(f2, dsqr, 1e-290);
-    const double y0 = rsqrt_seed(q);
+    double q, f2;
+    if (FLAVOR & 4) {
+        f2 = dsqr * dsqr;
+        q = f2 * dsqr;
+    } else {
+        const double mindist = b.r + rj;
+        const double mindsqr = mindist * mindist;
+        const double forced = __longlong_as_double(max(__double_as_longlong(dsqr), __double_as_longlong(mindsqr)));
+        if (FLAVOR & 2) minhi = __double2hiint(dsqr);   // combined by the caller
+        else b.minhi = min(b.minhi, __double2hiint(dsqr));
+        f2 = forced * forced;
+        q = fma(f2, dsqr, 1e-290);
+    }
+    const double y0 = (FLAVOR & 1) ? rsqrt_seed_donor(q, f2) : rsqrt_seed(q);
     const double t = q * y0;
     const double e = fma(-t, y0, 1.0);
     const double p = fma(e, 0.375, 0.5);
@@ -84,9 +104,9 @@ __device__ __forceinline__ double warp_sum(double v)
     return v;
 }
 
-template <int IB, bool GUARD, int UNROLL>
+template <int IB, bool GUARD, int UNROLL, int FLAVOR>
 __device__ __forceinline__ void sym_group(SymBody (&b)[IB], const double2 *tp, const double2 *tm, int g, int cnt,
-                                          int lane, double2 *col)
+                                          int lane, double2 *col, int &minhi)
 {
     double cx = 0.0, cy = 0.0;
     const int src = (lane + 1) & 31;
@@ -94,6 +114,7 @@ __device__ __forceinline__ void sym_group(SymBody (&b)[IB], const double2 *tp, c
     for (int r = 0; r < 32; ++r) {
         const int jj = g + ((lane + r) & 31);
         double2 pj, qj;
+        int hi[IB];
         if (GUARD && jj >= cnt) {
             pj = make_double2(-1.0e6, -1.0e6);   // beyond the last body: massless, far away, never stored
             qj = make_double2(0.0, 1.0);
@@ -102,7 +123,18 @@ __device__ __forceinline__ void sym_group(SymBody (&b)[IB], const double2 *tp, c
             qj = tm[jj];
         }
 #pragma unroll
-        for (int k = 0; k < IB; ++k) pair_sym(b[k], pj.x, pj.y, qj.x, qj.y, cx, cy);
+        for (int k = 0; k < IB; ++k) {
+            if ((FLAVOR & 6) == 2) {
+                pair_sym<FLAVOR>(b[k], pj.x, pj.y, qj.x, qj.y, cx, cy, hi[k]);
+            } else {
+                pair_sym<FLAVOR>(b[k], pj.x, pj.y, qj.x, qj.y, cx, cy, minhi);
+            }
+        }
+        if ((FLAVOR & 6) == 2) {
+#pragma unroll
+            for (int k = 0; k + 1 < IB; k += 2) minhi = __vimin3_s32(minhi, hi[k], hi[k + 1]);
+            if (IB & 1) minhi = min(minhi, hi[IB - 1]);
+        }
         cx = __shfl_sync(0xffffffffu, cx, src);
         cy = __shfl_sync(0xffffffffu, cy, src);
     }
@@ -144,7 +176,7 @@ __device__ __noinline__ double sym_col_rescan(const double2 *pos, const double2 
     return c;
 }
 
-template <int SYM_THREADS, int SYM_IB, int MINB = 1, int UNROLL = 4>
+template <int SYM_THREADS, int SYM_IB, int MINB = 1, int UNROLL = 4, int FLAVOR = 0>
 __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const SymArgs a)
 {
     static_assert(SYM_RB == SYM_THREADS * SYM_IB, "row block = threads x bodies per thread");
@@ -190,6 +222,7 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
 
     SymBody b[SYM_IB];
     int idx[SYM_IB];
+    int minhi = 0x7fffffff;
 #pragma unroll
     for (int k = 0; k < SYM_IB; ++k) {
         idx[k] = i0 + tid + k * SYM_THREADS;
@@ -232,11 +265,16 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
             // exactly once and after 32 steps lane l holds the warp's complete reaction sum for j = g + l:
             // no reduction tree, no atomics, fixed order.
             if (cnt == TILE_J) {
-                for (int g = 0; g < TILE_J; g += 32) sym_group<SYM_IB, false, UNROLL>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J);
+                for (int g = 0; g < TILE_J; g += 32) sym_group<SYM_IB, false, UNROLL, FLAVOR>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J, minhi);
             } else {
-                for (int g = 0; g < cnt; g += 32) sym_group<SYM_IB, true, UNROLL>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J);
+                for (int g = 0; g < cnt; g += 32) sym_group<SYM_IB, true, UNROLL, FLAVOR>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J, minhi);
             }
             bool hit = false;
+            if ((FLAVOR & 2) && minhi == 0) {
+#pragma unroll
+                for (int k = 0; k < SYM_IB; ++k) b[k].minhi = 0;
+                minhi = 0x7fffffff;
+            }
 #pragma unroll
             for (int k = 0; k < SYM_IB; ++k) {
                 if (b[k].minhi == 0) {

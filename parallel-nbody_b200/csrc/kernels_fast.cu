@@ -62,6 +62,11 @@ int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream
     case 4: NB_SYM_LAUNCH(128, 4, 1, 2) break;
     case 5: NB_SYM_LAUNCH(128, 4, 1, 8) break;
     case 6: NB_SYM_LAUNCH(128, 4, 5, 2) break;
+    case 11: NB_SYM_LAUNCH(128, 4, 1, 4, 1) break;
+    case 12: NB_SYM_LAUNCH(128, 4, 1, 4, 2) break;
+    case 13: NB_SYM_LAUNCH(128, 4, 1, 4, 3) break;
+    case 14: NB_SYM_LAUNCH(128, 4, 1, 4, 4) break;   // timing experiment only: every tile as far field
+    case 15: NB_SYM_LAUNCH(128, 4, 1, 4, 5) break;   // timing experiment only
     }
 #undef NB_SYM_LAUNCH
     return 0;
