@@ -324,6 +324,10 @@ def main():
     algo_tflops = 10.0 * launch_pairs / launch_s / 1e12   # reference flop model: 10 per directed pair
     desc = g.describe()
     ipp = desc.get("fp64_instr_per_pair") or None
+    far = g.far_fraction() if desc.get("cell_order") else 0.0
+    if ipp and far > 0.0:
+        # far-field tiles issue 17 FP64-pipe instructions per unordered pair instead of 19 (forces_sym.cuh)
+        ipp = ipp * (1.0 - far) + 8.5 * far
     roofline = {"bound": "fp64", "achieved": algo_tflops, "peak": peak_tf, "unit": "TFLOP/s",
                 "frac": algo_tflops / peak_tf, "traffic": None,
                 "peak_source": "measured live: nbody_gpu_fp64_peak DFMA kernel on this GPU "
@@ -333,6 +337,7 @@ def main():
                 "kernel_share_of_step": force_ms / t_ms,
                 "algorithmic_flops_per_pair": 10, "pairs_per_launch": launch_pairs}
     if ipp:
+        roofline["far_field_fraction"] = far
         roofline["fp64_pipe_instr_per_pair"] = ipp
         roofline["pipe_frac"] = ipp * (launch_pairs / launch_s) / (peak_tf * 1e12 / 2.0)
 

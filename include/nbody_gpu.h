@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define NBODY_GPU_ABI_VERSION 1
+#define NBODY_GPU_ABI_VERSION 2
 
 enum {
     NBODY_GPU_OK = 0,
@@ -67,6 +67,9 @@ typedef struct nbody_gpu_cfg {
                        -1 = directed evaluation only, 0 = library default (symmetric on one GPU for n >= 8192) */
     int p2p;        /* sharded symmetric fast mode: 0 = fuse the per-step exchange into the kernels over NVLink peer
                        memory when the GPUs can map each other (else ncclAllGather), 1 = require it, -1 = NCCL only */
+    int sort;       /* symmetric fast mode: 0 = library default (device arrays kept in cell order for n >= 16384 so that
+                       most tiles take the far-field form of the pair; invisible to the caller: every entry point
+                       speaks the caller's body order), 1 = always, -1 = keep creation order */
 } nbody_gpu_cfg;
 
 /* Replaces calloc(world) + initialize_simulation_data + MPI_Bcast
@@ -115,6 +118,11 @@ int nbody_gpu_fetch(nbody_gpu *h, double *x, double *y, double *xf, double *yf,
  * disc of radius R+0.5 covers the pixel gives the tint, empty space is black.  Headless: a device buffer,
  * copied to the host; the driver writes it behind the P6 header when secs_per_update > 0. */
 int nbody_gpu_render(nbody_gpu *h, unsigned char *rgb);
+
+/* Fraction of the symmetric kernel's pair evaluations (tiles above the diagonal) that currently take the
+ * far-field form (no clamp, 17 instead of 19 FP64-pipe instructions); 0 when the handle is not in cell order.
+ * For bench.py's instruction accounting.  Synchronous. */
+int nbody_gpu_far_fraction(nbody_gpu *h, double *fraction);
 
 int nbody_gpu_sync(nbody_gpu *h);
 void nbody_gpu_destroy(nbody_gpu *h);

@@ -32,7 +32,8 @@ class _Cfg(ctypes.Structure):
     _fields_ = [("n", ctypes.c_int), ("xdim", ctypes.c_int), ("ydim", ctypes.c_int),
                 ("mode", ctypes.c_int), ("ngpus", ctypes.c_int), ("device", ctypes.c_int),
                 ("rank", ctypes.c_int), ("nranks", ctypes.c_int), ("nccl_id", ctypes.c_void_p),
-                ("jsplit", ctypes.c_int), ("use_graph", ctypes.c_int), ("symmetric", ctypes.c_int), ("p2p", ctypes.c_int)]
+                ("jsplit", ctypes.c_int), ("use_graph", ctypes.c_int), ("symmetric", ctypes.c_int), ("p2p", ctypes.c_int),
+                ("sort", ctypes.c_int)]
 
 
 _lib = None
@@ -63,6 +64,7 @@ def lib():
     L.nbody_gpu_forces.argtypes = [vp, _dp, _dp]
     L.nbody_gpu_fetch.argtypes = [vp] + [odp] * 6
     L.nbody_gpu_render.argtypes = [vp, np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")]
+    L.nbody_gpu_far_fraction.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     L.nbody_gpu_sync.argtypes = [vp]
     L.nbody_gpu_destroy.argtypes = [vp]
     L.nbody_gpu_destroy.restype = None
@@ -125,7 +127,7 @@ class NBodyGPU:
     """One N-body world on the GPU(s). Arrays are host numpy float64 of length n."""
 
     def __init__(self, x, y, xv, yv, mass, radius, xdim=1024, ydim=768, mode=MODE_EXACT,
-                 ngpus=1, device=-1, rank=0, nranks=1, nccl_id=None, jsplit=0, use_graph=0, symmetric=0, p2p=0):
+                 ngpus=1, device=-1, rank=0, nranks=1, nccl_id=None, jsplit=0, use_graph=0, symmetric=0, p2p=0, sort=0):
         x, y, xv, yv, mass, radius = map(_f64, (x, y, xv, yv, mass, radius))
         self.n = int(x.shape[0])
         for a in (y, xv, yv, mass, radius):
@@ -133,7 +135,7 @@ class NBodyGPU:
                 raise ValueError("all body arrays must have the same length")
         self._id = ctypes.create_string_buffer(nccl_id, NCCL_ID_BYTES) if nccl_id else None
         cfg = _Cfg(self.n, xdim, ydim, mode, ngpus, device, rank, nranks,
-                   ctypes.cast(self._id, ctypes.c_void_p) if self._id else None, jsplit, use_graph, symmetric, p2p)
+                   ctypes.cast(self._id, ctypes.c_void_p) if self._id else None, jsplit, use_graph, symmetric, p2p, sort)
         self._h = ctypes.c_void_p()
         _check(lib().nbody_gpu_init(ctypes.byref(self._h), ctypes.byref(cfg), x, y, xv, yv, mass, radius))
 
@@ -172,13 +174,19 @@ class NBodyGPU:
         _check(lib().nbody_gpu_render(self._h, img))
         return img
 
+    def far_fraction(self):
+        """Share of the symmetric kernel's pair evaluations currently in far-field tiles (0 if not in cell order)."""
+        f = ctypes.c_double()
+        _check(lib().nbody_gpu_far_fraction(self._h, ctypes.byref(f)))
+        return f.value
+
     def sync(self):
         _check(lib().nbody_gpu_sync(self._h))
 
     def describe(self):
         import json
-        buf = ctypes.create_string_buffer(512)
-        lib().nbody_gpu_describe(self._h, buf, 512)
+        buf = ctypes.create_string_buffer(1024)
+        lib().nbody_gpu_describe(self._h, buf, 1024)
         return json.loads(buf.value.decode())
 
     def launch_count(self):

@@ -10,6 +10,12 @@
 //     (row sum) and the reaction on body j is reduced over the 32 lanes by a shuffle
 //     butterfly, over the 8 warps through shared memory, and written ONCE per (block, j) to
 //     colpart[B][j] -- no atomics, fixed order, so the result is deterministic.
+// Far field: with the bodies in cell order (sort_kernels.cuh) most (row block, j tile) pairs are further apart
+// than any r_i + r_j of their bodies.  Every tile carries a bounding box (x/y range, largest radius; one more
+// TMA copy per tile); if the gap between the block's box and the tile's box is at least rmax_B + rmax_T the
+// clamp max(dsqr, mindsqr) is the identity for every pair of the tile and no two bodies can coincide, so the
+// tile runs the far-field form of the pair: 17 FP64-pipe instructions and no integer work.  The test uses the
+// same rounded operations as the pair itself (monotone), so it is exact and both forms give the same bits.
 // sym_reduce_kernel then folds the partial sums into SYM_V per-virtual-rank vectors (step_args.h) and
 // integrate_kernel adds those in a fixed order: the same bits on 1, 2, 4 or 8 GPUs.  Per unordered pair: 19 FP64-pipe instructions (13 shared, 3 per side)
 // + 1 MUFU + ~8 ALU/LSU + 0.3 SHFL, against 2 x (16 + ...) for the directed kernel.
@@ -141,7 +147,7 @@ __device__ __forceinline__ void sym_group(SymBody (&b)[IB], const double2 *tp, c
     col[g + lane] = make_double2(cx, cy);   // entries >= cnt are never read
 }
 
-constexpr int sym_smem_bytes(int threads) { return STAGES * TILE_J * 16 * 2 + (threads / 32) * TILE_J * 16 + 64; }
+constexpr int sym_smem_bytes(int threads) { return STAGES * TILE_J * 16 * 2 + (threads / 32) * TILE_J * 16 + (STAGES + 1) * SYM_BOX_DOUBLES * 8 + 64; }
 static_assert(SYM_RB % TILE_J == 0, "row blocks must be tile aligned");
 
 // Rare path, row side of a tile above the block (all j > i): + m_j / mindsqr for coincident j.
@@ -176,7 +182,7 @@ __device__ __noinline__ double sym_col_rescan(const double2 *pos, const double2 
     return c;
 }
 
-template <int SYM_THREADS, int SYM_IB, int MINB = 1, int UNROLL = 4, int FLAVOR = 0>
+template <int SYM_THREADS, int SYM_IB, int MINB = 1, int UNROLL = 4, int FLAVOR = 3, int FAR_FLAVOR = 5>
 __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const SymArgs a)
 {
     static_assert(SYM_RB == SYM_THREADS * SYM_IB, "row block = threads x bodies per thread");
@@ -185,7 +191,9 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     double2 *s_pos = reinterpret_cast<double2 *>(sym_smem);                 // [STAGES][TILE_J]
     double2 *s_mr = s_pos + STAGES * TILE_J;                                // [STAGES][TILE_J]
     double2 *s_col = s_mr + STAGES * TILE_J;                                // [SYM_WARPS][TILE_J]
-    uint64_t *s_full = reinterpret_cast<uint64_t *>(s_col + SYM_WARPS * TILE_J);
+    double *s_box = reinterpret_cast<double *>(s_col + SYM_WARPS * TILE_J);   // [STAGES][SYM_BOX_DOUBLES] tile boxes
+    double *s_bbox = s_box + STAGES * SYM_BOX_DOUBLES;                        // [SYM_BOX_DOUBLES] this row block's box
+    uint64_t *s_full = reinterpret_cast<uint64_t *>(s_bbox + SYM_BOX_DOUBLES);
     int *s_flag = reinterpret_cast<int *>(s_full + STAGES);                 // [2]
 
     const int tid = threadIdx.x;
@@ -206,15 +214,32 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
         s_flag[0] = 0;
         s_flag[1] = 0;
     }
+    if (tid == 32 && a.boxes) {
+        // bounding box of this row block = union of its tiles' boxes
+        const double *bb = a.boxes + static_cast<size_t>(i0 / TILE_J) * SYM_BOX_DOUBLES;
+        double bx0 = bb[0], by0 = bb[1], bx1 = bb[2], by1 = bb[3], brmax = bb[4];
+#pragma unroll
+        for (int t = 1; t < SYM_RB / TILE_J; ++t) {
+            if (i0 + t * TILE_J < a.n) {
+                bb += SYM_BOX_DOUBLES;
+                bx0 = fmin(bx0, bb[0]); by0 = fmin(by0, bb[1]);
+                bx1 = fmax(bx1, bb[2]); by1 = fmax(by1, bb[3]);
+                brmax = fmax(brmax, bb[4]);
+            }
+        }
+        s_bbox[0] = bx0; s_bbox[1] = by0; s_bbox[2] = bx1; s_bbox[3] = by1; s_bbox[4] = brmax;
+    }
     __syncthreads();
 
     auto issue = [&](int tile) {
         const int st = tile % STAGES;
         const int jb = j0 + tile * TILE_J;
         const uint32_t bytes = static_cast<uint32_t>(min(TILE_J, j1 - jb)) * sizeof(double2);
-        mbar_arrive_expect_tx(&s_full[st], 2 * bytes);
+        const uint32_t box_bytes = a.boxes ? SYM_BOX_DOUBLES * 8 : 0;
+        mbar_arrive_expect_tx(&s_full[st], 2 * bytes + box_bytes);
         tma_load_1d(s_pos + st * TILE_J, a.pos + jb, bytes, &s_full[st]);
         tma_load_1d(s_mr + st * TILE_J, a.mr + jb, bytes, &s_full[st]);
+        if (a.boxes) tma_load_1d(s_box + st * SYM_BOX_DOUBLES, a.boxes + static_cast<size_t>(jb / TILE_J) * SYM_BOX_DOUBLES, box_bytes, &s_full[st]);
     };
     if (tid == 0) {
         for (int t = 0; t < STAGES && t < ntiles; ++t) issue(t);
@@ -227,8 +252,9 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     for (int k = 0; k < SYM_IB; ++k) {
         idx[k] = i0 + tid + k * SYM_THREADS;
         const bool live = idx[k] < a.n;
-        const double2 p = live ? a.pos[idx[k]] : make_double2(0.0, 0.0);
-        const double2 q = live ? a.mr[idx[k]] : make_double2(0.0, 1.0);   // mass 0: no reaction from padding rows
+        // padding rows: massless (no reaction) and away from every body and from the padding columns
+        const double2 p = live ? a.pos[idx[k]] : make_double2(-2.0e6, -2.0e6);
+        const double2 q = live ? a.mr[idx[k]] : make_double2(0.0, 1.0);
         b[k].x = p.x; b[k].y = p.y; b[k].m = q.x; b[k].r = q.y;
         b[k].ax = 0.0; b[k].ay = 0.0;
         b[k].minhi = 0x7fffffff;
@@ -264,7 +290,24 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
             // accumulator of a j travels the other way (one lane down per step), so it meets every lane
             // exactly once and after 32 steps lane l holds the warp's complete reaction sum for j = g + l:
             // no reduction tree, no atomics, fixed order.
-            if (cnt == TILE_J) {
+            bool far = false;
+            if (a.boxes) {
+                // gap between the boxes against the largest r_i + r_j, in the pair's own operations:
+                // dx >= gx and dy >= gy for every pair, rounding is monotone, so dsqr >= gap2 >= md2 >= mindsqr
+                const double *tb = s_box + st * SYM_BOX_DOUBLES;
+                const double gx = fmax(0.0, fmax(tb[0] - s_bbox[2], s_bbox[0] - tb[2]));
+                const double gy = fmax(0.0, fmax(tb[1] - s_bbox[3], s_bbox[1] - tb[3]));
+                const double gap2 = fma(gx, gx, gy * gy);
+                const double md = s_bbox[4] + tb[4];
+                far = gap2 >= md * md;
+            }
+            if (far) {
+                if (cnt == TILE_J) {
+                    for (int g = 0; g < TILE_J; g += 32) sym_group<SYM_IB, false, UNROLL, FAR_FLAVOR>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J, minhi);
+                } else {
+                    for (int g = 0; g < cnt; g += 32) sym_group<SYM_IB, true, UNROLL, FAR_FLAVOR>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J, minhi);
+                }
+            } else if (cnt == TILE_J) {
                 for (int g = 0; g < TILE_J; g += 32) sym_group<SYM_IB, false, UNROLL, FLAVOR>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J, minhi);
             } else {
                 for (int g = 0; g < cnt; g += 32) sym_group<SYM_IB, true, UNROLL, FLAVOR>(b, tp, tm, g, cnt, lane, s_col + warp * TILE_J, minhi);

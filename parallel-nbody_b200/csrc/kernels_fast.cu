@@ -55,18 +55,11 @@ int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream
     if (variant == 1) threads = 256;
     const int smem = sym_smem_bytes(threads);
     switch (variant) {
-    default: NB_SYM_LAUNCH(128, 4) break;
+    default: NB_SYM_LAUNCH(128, 4) break;             // near flavour 3, far flavour 5
     case 1: NB_SYM_LAUNCH(256, 2) break;
-    case 2: NB_SYM_LAUNCH(128, 4, 5) break;
-    case 3: NB_SYM_LAUNCH(128, 4, 6) break;
     case 4: NB_SYM_LAUNCH(128, 4, 1, 2) break;
     case 5: NB_SYM_LAUNCH(128, 4, 1, 8) break;
-    case 6: NB_SYM_LAUNCH(128, 4, 5, 2) break;
-    case 11: NB_SYM_LAUNCH(128, 4, 1, 4, 1) break;
-    case 12: NB_SYM_LAUNCH(128, 4, 1, 4, 2) break;
-    case 13: NB_SYM_LAUNCH(128, 4, 1, 4, 3) break;
-    case 14: NB_SYM_LAUNCH(128, 4, 1, 4, 4) break;   // timing experiment only: every tile as far field
-    case 15: NB_SYM_LAUNCH(128, 4, 1, 4, 5) break;   // timing experiment only
+    case 10: NB_SYM_LAUNCH(128, 4, 1, 4, 0, 4) break;  // round-1 pair arithmetic
     }
 #undef NB_SYM_LAUNCH
     return 0;

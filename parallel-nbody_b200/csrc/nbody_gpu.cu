@@ -60,6 +60,16 @@ struct Shard {
     double2 *part = nullptr;
     double2 *colpart = nullptr;  // symmetric fast kernel: reaction partial sums [owned blocks][npad]
     double2 *vbuf = nullptr;     // symmetric fast kernel: per-virtual-rank force vectors [SYM_V][npad]
+    // cell order + far-field test of the symmetric kernel (kernels_sort.cu)
+    int *orig = nullptr;         // original index of slot s (identity until the first sort)
+    double *boxes = nullptr;     // [ceil(n/TILE_J)][SYM_BOX_DOUBLES] per-tile bounding boxes, rebuilt every step
+    double2 *mr0 = nullptr;      // (mass, radius) in original order, for set_state
+    unsigned long long *keys[2] = {nullptr, nullptr};
+    int *vals[2] = {nullptr, nullptr};
+    int *orig_tmp = nullptr;
+    void *sort_tmp = nullptr;
+    size_t sort_tmp_bytes = 0;
+    double2 *gat[4] = {nullptr, nullptr, nullptr, nullptr};   // gather targets of a re-sort; scratch for unsorting
     int v0 = 0, nv = SYM_V;      // virtual ranks owned by this shard
     PeerTable peers = {};        // fused peer-memory exchange (npeers = 0: not in use)
     unsigned long long *flags = nullptr;   // [2][MAX_PEERS] epoch words written by the peers
@@ -83,6 +93,12 @@ struct nbody_gpu {
     int nsplit = 1;              // fast mode: j-chunks
     int chunk = 0;               // fast mode: j-chunk length
     bool symmetric = false;      // fast mode: evaluate each unordered pair once (forces_sym_kernel)
+    bool sorted = false;         // symmetric: device arrays are kept in cell order (Shard::orig maps slots to bodies)
+    int sort_interval = 0;       // steps between re-sorts
+    long long since_sort = 0;    // steps since the last sort
+    long long sorts = 0;
+    std::vector<int> orig_host;  // host copy of orig, refreshed lazily
+    bool orig_host_valid = false;
     bool p2p = false;            // sharded symmetric: exchange fused into the kernels over peer memory (no NCCL per step)
     unsigned long long epoch = 0;
     int nblocks = 0;             // symmetric: number of SYM_RB row blocks
@@ -151,6 +167,17 @@ static void free_shard(Shard &s)
     if (s.frc) cudaFree(s.frc);
     if (s.part) cudaFree(s.part);
     if (s.colpart) cudaFree(s.colpart);
+    if (s.orig) cudaFree(s.orig);
+    if (s.boxes) cudaFree(s.boxes);
+    if (s.mr0) cudaFree(s.mr0);
+    if (s.orig_tmp) cudaFree(s.orig_tmp);
+    if (s.sort_tmp) cudaFree(s.sort_tmp);
+    for (int k = 0; k < 2; ++k) {
+        if (s.keys[k]) cudaFree(s.keys[k]);
+        if (s.vals[k]) cudaFree(s.vals[k]);
+    }
+    for (int k = 0; k < 4; ++k)
+        if (s.gat[k]) cudaFree(s.gat[k]);
     for (void *m : s.ipc_opened) cudaIpcCloseMemHandle(m);
     s.ipc_opened.clear();
     if (s.vbuf) cudaFree(s.vbuf);
@@ -223,11 +250,13 @@ static void enqueue_forces(nbody_gpu *h, Shard &s, int slot)
         a.mr = s.mr;
         a.rowpart = s.part;
         a.colpart = s.colpart;
+        a.boxes = s.boxes;
         a.n = h->n;
         a.npad = h->npad;
         a.chunk = h->chunk;
         a.v0 = s.v0;
         a.nv = s.nv;
+        if (s.boxes) launch_tile_boxes(s.pos[slot], s.mr, h->n, s.boxes, s.stream);
         launch_forces_sym(a, s.nblocks_owned, h->nsplit, s.stream);
     } else {
         launch_forces_fast(force_args(h, s, slot), h->nsplit, s.stream);
@@ -291,6 +320,62 @@ static int allgather(nbody_gpu *h, int which)
     return NBODY_GPU_OK;
 }
 
+// Put every local shard's arrays into cell order (kernels_sort.cu).  All devices hold the same positions, so
+// they all arrive at the same permutation without talking to each other; with the fused peer exchange the
+// velocities and last forces live sharded and are gathered first (`gather`).
+static int resort(nbody_gpu *h, bool gather)
+{
+    if (!h->sorted) return NBODY_GPU_OK;
+    if (gather && h->sharded && h->p2p) {
+        int rc = allgather(h, AG_VEL);
+        if (!rc) rc = allgather(h, AG_FRC);
+        if (rc) return rc;
+    }
+    const double scale = 65535.0 / static_cast<double>(h->cfg.xdim > h->cfg.ydim ? h->cfg.xdim : h->cfg.ydim);
+    const size_t bytes = sizeof(double2) * static_cast<size_t>(h->n);
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        SortArgs a;
+        a.pos = s.pos[h->cur];
+        a.orig = s.orig;
+        a.n = h->n;
+        a.scale = scale;
+        a.keys_in = s.keys[0];
+        a.keys_out = s.keys[1];
+        a.vals_in = s.vals[0];
+        a.vals_out = s.vals[1];
+        a.temp = s.sort_tmp;
+        a.temp_bytes = s.sort_tmp_bytes;
+        const int e = launch_sort(a, s.stream);
+        if (e) return fail(NBODY_GPU_ECUDA, "radix sort failed: %s", cudaGetErrorString(static_cast<cudaError_t>(e)));
+        PermuteArgs p;
+        p.src_slot = s.vals[1];
+        p.pos_in = s.pos[h->cur]; p.mr_in = s.mr; p.vel_in = s.vel; p.frc_in = s.frc; p.orig_in = s.orig;
+        p.pos_out = s.gat[0]; p.mr_out = s.gat[1]; p.vel_out = s.gat[2]; p.frc_out = s.gat[3]; p.orig_out = s.orig_tmp;
+        p.n = h->n;
+        launch_permute(p, s.stream);
+        NB_CUDA(cudaMemcpyAsync(s.pos[h->cur], s.gat[0], bytes, cudaMemcpyDeviceToDevice, s.stream));
+        NB_CUDA(cudaMemcpyAsync(s.mr, s.gat[1], bytes, cudaMemcpyDeviceToDevice, s.stream));
+        NB_CUDA(cudaMemcpyAsync(s.vel, s.gat[2], bytes, cudaMemcpyDeviceToDevice, s.stream));
+        NB_CUDA(cudaMemcpyAsync(s.frc, s.gat[3], bytes, cudaMemcpyDeviceToDevice, s.stream));
+        NB_CUDA(cudaMemcpyAsync(s.orig, s.orig_tmp, sizeof(int) * static_cast<size_t>(h->n), cudaMemcpyDeviceToDevice, s.stream));
+        NB_CUDA(cudaGetLastError());
+    }
+    h->launches[2] += static_cast<long long>(h->shards.size()) * 3;
+    h->since_sort = 0;
+    h->sorts += 1;
+    h->orig_host_valid = false;
+    return NBODY_GPU_OK;
+}
+
+// The re-sort schedule is a function of the step count alone, so results do not depend on how calls to
+// nbody_gpu_step are split or on the number of GPUs.
+static int maybe_resort(nbody_gpu *h)
+{
+    if (h->sorted && h->since_sort >= h->sort_interval) return resort(h, true);
+    return NBODY_GPU_OK;
+}
+
 // Optional per-phase event hooks for nbody_gpu_step_profiled: mark(shard index, phase 0..4).
 struct StepMarks {
     virtual int mark(size_t shard, int phase) = 0;
@@ -312,6 +397,10 @@ static int run_one_step(nbody_gpu *h, StepMarks *marks)
             if (rc_) return rc_;                                \
         }                                                       \
     }
+    {
+        int rc = maybe_resort(h);
+        if (rc) return rc;
+    }
     NB_MARK(0)
     h->epoch += 1;
     for (Shard &s : h->shards) {
@@ -319,6 +408,7 @@ static int run_one_step(nbody_gpu *h, StepMarks *marks)
         enqueue_forces(h, s, h->cur);
     }
     h->launches[0] += static_cast<long long>(nsh);
+    if (h->sorted) h->launches[2] += static_cast<long long>(nsh);   // tile_boxes_kernel
     NB_MARK(1)
     if (h->symmetric) {
         for (Shard &s : h->shards) {
@@ -360,6 +450,7 @@ static int run_one_step(nbody_gpu *h, StepMarks *marks)
     NB_MARK(5)
 #undef NB_MARK
     h->cur ^= 1;   // the reference's world->old ^= 1 (nbody-seq.c:464)
+    h->since_sort += 1;
     return NBODY_GPU_OK;
 }
 
@@ -418,6 +509,14 @@ static int do_steps(nbody_gpu *h, int steps)
         Shard &s = h->shards[0];
         NB_CUDA(cudaSetDevice(s.device));
         while (left >= h->graph_steps) {
+            if (h->sorted && h->since_sort + h->graph_steps > h->sort_interval) {
+                // a re-sort is due before or inside the next graph launch: single steps until it has happened
+                int rc = run_one_step(h, nullptr);
+                if (rc) return rc;
+                left -= 1;
+                NB_CUDA(cudaSetDevice(s.device));
+                continue;
+            }
             if (!s.graph[h->cur]) {
                 int rc = build_graph(h, s, h->cur);
                 if (rc) return rc;
@@ -425,7 +524,8 @@ static int do_steps(nbody_gpu *h, int steps)
             NB_CUDA(cudaGraphLaunch(s.graph[h->cur], s.stream));
             h->launches[0] += h->graph_steps;
             h->launches[1] += h->graph_steps;
-            if (h->symmetric) h->launches[2] += h->graph_steps;
+            if (h->symmetric) h->launches[2] += h->graph_steps * (h->sorted ? 2 : 1);
+            h->since_sort += h->graph_steps;
             left -= h->graph_steps;   // graph_steps is even: h->cur is unchanged
         }
     }
@@ -629,6 +729,11 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
     h->symmetric = cfg->mode == NBODY_GPU_MODE_FAST && (SYM_V % P == 0) &&
                    (cfg->symmetric > 0 || (cfg->symmetric == 0 && h->n >= 8192));
     h->nblocks = (h->n + SYM_RB - 1) / SYM_RB;
+    h->sorted = h->symmetric && (cfg->sort > 0 || (cfg->sort == 0 && h->n >= 16384));
+    h->sort_interval = 256;
+    if (const char *e = getenv("NBODY_SORT_INTERVAL")) {   // development knob
+        if (atoi(e) > 0) h->sort_interval = atoi(e);
+    }
     if (h->symmetric) choose_split_sym(h->n, cfg->jsplit, &h->nsplit, &h->chunk);
     else if (cfg->mode == NBODY_GPU_MODE_FAST) choose_split(h->n, cfg->jsplit, &h->nsplit, &h->chunk);
     else { h->nsplit = 1; h->chunk = h->n; }
@@ -674,6 +779,20 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
                 NB_CUDA(cudaMalloc(&s.vbuf, bytes * SYM_V));
                 NB_CUDA(cudaMemsetAsync(s.vbuf, 0, bytes * SYM_V, s.stream));
             }
+            if (h->sorted) {
+                const size_t ntiles = static_cast<size_t>((h->n + TILE_J - 1) / TILE_J);
+                NB_CUDA(cudaMalloc(&s.boxes, ntiles * SYM_BOX_DOUBLES * sizeof(double)));
+                NB_CUDA(cudaMalloc(&s.orig, sizeof(int) * static_cast<size_t>(h->npad)));
+                NB_CUDA(cudaMalloc(&s.orig_tmp, sizeof(int) * static_cast<size_t>(h->npad)));
+                NB_CUDA(cudaMalloc(&s.mr0, bytes));
+                for (int q = 0; q < 2; ++q) {
+                    NB_CUDA(cudaMalloc(&s.keys[q], sizeof(unsigned long long) * static_cast<size_t>(h->npad)));
+                    NB_CUDA(cudaMalloc(&s.vals[q], sizeof(int) * static_cast<size_t>(h->npad)));
+                }
+                for (int q = 0; q < 4; ++q) NB_CUDA(cudaMalloc(&s.gat[q], bytes));
+                s.sort_tmp_bytes = sort_temp_bytes(h->n);
+                NB_CUDA(cudaMalloc(&s.sort_tmp, s.sort_tmp_bytes ? s.sort_tmp_bytes : 16));
+            }
         }
     }
     NB_CUDA(cudaMallocHost(&h->stage, sizeof(double2) * static_cast<size_t>(h->npad)));
@@ -700,6 +819,14 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
     if (!rc) rc = upload(h, &Shard::mr, 0, mass, radius);
     if (!rc) rc = upload(h, &Shard::vel, 0, xv, yv);
     h->cur = 0;
+    if (!rc && h->sorted) {
+        for (Shard &s : h->shards) {
+            NB_CUDA(cudaSetDevice(s.device));
+            NB_CUDA(cudaMemcpyAsync(s.mr0, s.mr, sizeof(double2) * static_cast<size_t>(h->npad), cudaMemcpyDeviceToDevice, s.stream));
+            launch_iota(s.orig, h->npad, s.stream);
+        }
+        rc = resort(h, false);
+    }
     if (!rc && h->sharded && h->symmetric && cfg->p2p >= 0) {
         rc = setup_p2p(h);
         if (!rc && !h->p2p && cfg->p2p > 0) rc = fail(NBODY_GPU_ECUDA, "peer-memory exchange requested but peer access is unavailable");
@@ -742,6 +869,16 @@ int nbody_gpu_set_state(nbody_gpu *h, const double *x, const double *y, const do
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
         NB_CUDA(cudaMemsetAsync(s.frc, 0, sizeof(double2) * static_cast<size_t>(h->npad), s.stream));
+        if (h->sorted) {   // the upload is in original order: back to the identity permutation, then sort again
+            NB_CUDA(cudaMemcpyAsync(s.mr, s.mr0, sizeof(double2) * static_cast<size_t>(h->npad), cudaMemcpyDeviceToDevice, s.stream));
+            launch_iota(s.orig, h->npad, s.stream);
+        }
+    }
+    if (h->sorted) {
+        rc = resort(h, false);
+        if (rc) return rc;
+        rc = sync_all(h);   // with the fused peer exchange no device may run ahead into a step before all have sorted
+        if (rc) return rc;
     }
     return NBODY_GPU_OK;
 }
@@ -863,7 +1000,20 @@ static int download(nbody_gpu *h, const double2 *src, cudaStream_t st, double *a
 {
     if (!a && !b) return NBODY_GPU_OK;
     NB_CUDA(cudaMemcpyAsync(h->stage, src, sizeof(double2) * static_cast<size_t>(h->n), cudaMemcpyDeviceToHost, st));
+    if (h->sorted && !h->orig_host_valid) {
+        h->orig_host.resize(static_cast<size_t>(h->n));
+        NB_CUDA(cudaMemcpyAsync(h->orig_host.data(), h->shards[0].orig, sizeof(int) * static_cast<size_t>(h->n), cudaMemcpyDeviceToHost, st));
+        h->orig_host_valid = true;
+    }
     NB_CUDA(cudaStreamSynchronize(st));
+    if (h->sorted) {   // slot order -> the caller's body order
+        const int *orig = h->orig_host.data();
+        for (int s = 0; s < h->n; ++s) {
+            if (a) a[orig[s]] = h->stage[s].x;
+            if (b) b[orig[s]] = h->stage[s].y;
+        }
+        return NBODY_GPU_OK;
+    }
     for (int i = 0; i < h->n; ++i) {
         if (a) a[i] = h->stage[i].x;
         if (b) b[i] = h->stage[i].y;
@@ -933,19 +1083,64 @@ int nbody_gpu_describe(const nbody_gpu *h, char *buf, int len)
     const char *kernel = !fast ? "forces_kernel<EXACT>" : h->symmetric ? "forces_sym_kernel<128,4>" : "forces_fast_kernel<2,4,1,true>";
     // FP64-pipe instructions per directed pair-interaction (SASS counts): the symmetric
     // kernel issues 19 per unordered pair = 2 interactions; exact mode is not a fixed count (divisions, branches)
+    // (19 near, 17 in far-field tiles: see nbody_gpu_far_fraction)
     const double ipp = !fast ? 0.0 : h->symmetric ? 9.5 : 16.0;
-    char tmp[512];
+    char tmp[640];
     const int need = snprintf(tmp, sizeof tmp,
                               "{\"mode\": \"%s\", \"kernel\": \"%s\", \"symmetric\": %s, \"nsplit\": %d, \"chunk\": %d, "
-                              "\"row_blocks\": %d, \"shards\": %d, \"graph_steps\": %d, \"exchange\": \"%s\", \"fp64_instr_per_pair\": %.1f}",
+                              "\"row_blocks\": %d, \"shards\": %d, \"graph_steps\": %d, \"exchange\": \"%s\", \"fp64_instr_per_pair\": %.1f, "
+                              "\"cell_order\": %s, \"sort_interval\": %d, \"sorts\": %lld}",
                               fast ? "fast" : "exact", kernel, h->symmetric ? "true" : "false", h->nsplit, h->chunk,
                               h->symmetric ? h->nblocks : 0, h->nshards_total, h->sharded ? 0 : h->graph_steps,
-                              !h->sharded ? "none" : h->p2p ? "peer-memory stores + signal/wait kernels" : "ncclAllGather", ipp);
+                              !h->sharded ? "none" : h->p2p ? "peer-memory stores + signal/wait kernels" : "ncclAllGather", ipp,
+                              h->sorted ? "true" : "false", h->sorted ? h->sort_interval : 0, h->sorts);
     if (buf && len > 0) {
         strncpy(buf, tmp, static_cast<size_t>(len) - 1);
         buf[len - 1] = 0;
     }
     return need + 1;
+}
+
+int nbody_gpu_far_fraction(nbody_gpu *h, double *fraction)
+{
+    if (!h || !fraction) return fail(NBODY_GPU_EINVAL, "NULL argument");
+    *fraction = 0.0;
+    if (!h->sorted) return NBODY_GPU_OK;
+    int rc = sync_all(h);
+    if (rc) return rc;
+    Shard &s = h->shards[0];
+    NB_CUDA(cudaSetDevice(s.device));
+    const int ntiles = (h->n + TILE_J - 1) / TILE_J;
+    std::vector<double> bx(static_cast<size_t>(ntiles) * SYM_BOX_DOUBLES);
+    launch_tile_boxes(s.pos[h->cur], s.mr, h->n, s.boxes, s.stream);
+    NB_CUDA(cudaMemcpyAsync(bx.data(), s.boxes, bx.size() * sizeof(double), cudaMemcpyDeviceToHost, s.stream));
+    NB_CUDA(cudaStreamSynchronize(s.stream));
+    // the same walk and the same test as forces_sym_kernel: tiles above each row block
+    const int tiles_per_block = SYM_RB / TILE_J;
+    double far = 0.0, all = 0.0;
+    for (int B = 0; B < h->nblocks; ++B) {
+        double b[5];
+        for (int t = 0; t < tiles_per_block && B * tiles_per_block + t < ntiles; ++t) {
+            const double *q = &bx[static_cast<size_t>(B * tiles_per_block + t) * SYM_BOX_DOUBLES];
+            if (t == 0) { for (int k = 0; k < 5; ++k) b[k] = q[k]; continue; }
+            b[0] = q[0] < b[0] ? q[0] : b[0]; b[1] = q[1] < b[1] ? q[1] : b[1];
+            b[2] = q[2] > b[2] ? q[2] : b[2]; b[3] = q[3] > b[3] ? q[3] : b[3];
+            b[4] = q[4] > b[4] ? q[4] : b[4];
+        }
+        for (int T = (B + 1) * tiles_per_block; T < ntiles; ++T) {
+            const double *q = &bx[static_cast<size_t>(T) * SYM_BOX_DOUBLES];
+            double gx = q[0] - b[2] > b[0] - q[2] ? q[0] - b[2] : b[0] - q[2];
+            double gy = q[1] - b[3] > b[1] - q[3] ? q[1] - b[3] : b[1] - q[3];
+            if (gx < 0.0) gx = 0.0;
+            if (gy < 0.0) gy = 0.0;
+            const double md = b[4] + q[4];
+            const int cnt = (T + 1) * TILE_J <= h->n ? TILE_J : h->n - T * TILE_J;
+            all += cnt;
+            if (gx * gx + gy * gy >= md * md) far += cnt;
+        }
+    }
+    if (all > 0.0) *fraction = far / all;
+    return NBODY_GPU_OK;
 }
 
 int nbody_gpu_render(nbody_gpu *h, unsigned char *rgb)
@@ -958,7 +1153,13 @@ int nbody_gpu_render(nbody_gpu *h, unsigned char *rgb)
     unsigned char *img = nullptr;
     NB_CUDA(cudaMalloc(&owner, npix * sizeof(int)));
     NB_CUDA(cudaMalloc(&img, npix * 3));
-    launch_render(s.pos[h->cur], s.mr, h->n, h->cfg.xdim, h->cfg.ydim, owner, img, s.stream);
+    const double2 *rpos = s.pos[h->cur], *rmr = s.mr;
+    if (h->sorted) {   // the lowest ORIGINAL index wins a pixel (nbody-seq.c:336-347): paint from body order
+        launch_unsort(s.pos[h->cur], s.orig, s.gat[0], h->n, s.stream);
+        rpos = s.gat[0];
+        rmr = s.mr0;
+    }
+    launch_render(rpos, rmr, h->n, h->cfg.xdim, h->cfg.ydim, owner, img, s.stream);
     h->launches[2] += 3;
     cudaError_t e = cudaMemcpyAsync(rgb, img, npix * 3, cudaMemcpyDeviceToHost, s.stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);

@@ -23,12 +23,14 @@ struct ForceArgs {
 };
 
 constexpr int SYM_RB = 512;         // rows per block of the symmetric (evaluate-each-pair-once) kernel
+constexpr int SYM_BOX_DOUBLES = 8;  // per-tile bounding box: xmin ymin xmax ymax rmax + padding (one 64-byte bulk copy)
 
 struct SymArgs {
     const double2 *pos;
     const double2 *mr;
     double2 *rowpart;     // [nsplit][npad]  row-side partial sums
     double2 *colpart;     // [nblocks][npad] reaction (column-side) partial sums, valid for j >= (B+1)*SYM_RB
+    const double *boxes;  // [ceil(n/TILE_J)][8] per-tile bounding boxes (xmin ymin xmax ymax rmax . . .), or nullptr
     int n;
     int npad;
     int chunk;            // j-chunk length, a multiple of SYM_RB
@@ -97,6 +99,32 @@ struct IntegrateArgs {
     double2 *peer_pos_new[MAX_PEERS];   // fused position exchange: also store pos_new[i] here (npeers entries)
     int npeers;                         // 0 = store to pos_new only
 };
+
+// Cell order (kernels_sort.cu): key = Hilbert index of the position << 32 | original index, value = slot.
+struct SortArgs {
+    const double2 *pos;
+    const int *orig;
+    int n;
+    double scale;                   // world coordinate -> 16-bit cell coordinate
+    unsigned long long *keys_in, *keys_out;
+    int *vals_in, *vals_out;
+    void *temp;
+    size_t temp_bytes;
+};
+struct PermuteArgs {
+    const int *src_slot;            // sorted values: new slot t takes old slot src_slot[t]
+    const double2 *pos_in, *mr_in, *vel_in, *frc_in;
+    const int *orig_in;
+    double2 *pos_out, *mr_out, *vel_out, *frc_out;
+    int *orig_out;
+    int n;
+};
+size_t sort_temp_bytes(int n);
+int launch_sort(const SortArgs &a, cudaStream_t st);   // returns cudaError_t
+void launch_permute(const PermuteArgs &a, cudaStream_t st);
+void launch_unsort(const double2 *in, const int *orig, double2 *out, int n, cudaStream_t st);
+void launch_iota(int *orig, int n, cudaStream_t st);
+void launch_tile_boxes(const double2 *pos, const double2 *mr, int n, double *boxes, cudaStream_t st);
 
 // launchers, defined in kernels_exact.cu / kernels_fast.cu
 void launch_forces_exact(const ForceArgs &a, cudaStream_t st);

@@ -1,0 +1,176 @@
+"""Cell order (kernels_sort.cu) + the far-field form of the symmetric fast kernel.
+
+The library may keep its device arrays sorted by the Hilbert index of the positions so that most
+(row block, j tile) pairs are provably unclamped and take a cheaper form of the pair.  None of that may be
+visible through the C ABI: every entry point speaks the caller's body order, results stay within the fast
+mode's stated tolerance of the reference's math (oracle, libm trig), and they are a function of the inputs
+and the step count only -- not of how nbody_gpu_step calls are split, nor of the number of GPUs."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+POS_RTOL = 1e-12
+VEL_RTOL = 1e-10
+
+
+def make(nb, b, **kw):
+    return nb.NBodyGPU(b.x, b.y, b.xv, b.yv, b.mass, b.radius, mode=nb.MODE_FAST, symmetric=1, **kw)
+
+
+def bits_equal(a, c):
+    return all(np.array_equal(u.view(np.uint64), v.view(np.uint64)) for u, v in zip(a, c))
+
+
+@pytest.mark.parametrize("n,steps", [(3000, 5), (20000, 4), (16384 + 77, 3)])
+def test_cell_order_within_tolerance_of_reference_math(nb, oracle, n, steps):
+    b = oracle.init_bodies(n)
+    g = make(nb, b, sort=1)
+    d = g.describe()
+    assert d["cell_order"] is True and d["sorts"] == 1
+    g.step(steps)
+    x, y, xf, yf, xv, yv = g.fetch()
+    ref = b.copy()
+    oracle.run(ref, steps, trig=0, threads=8)
+    np.testing.assert_allclose(x, ref.x, rtol=POS_RTOL, atol=1e-12)
+    np.testing.assert_allclose(y, ref.y, rtol=POS_RTOL, atol=1e-12)
+    np.testing.assert_allclose(xv, ref.xv, rtol=VEL_RTOL, atol=1e-12)
+    np.testing.assert_allclose(yv, ref.yv, rtol=VEL_RTOL, atol=1e-12)
+    fmax = max(np.abs(ref.xf).max(), np.abs(ref.yf).max())
+    assert np.abs(xf - ref.xf).max() <= 1e-8 * fmax and np.abs(yf - ref.yf).max() <= 1e-8 * fmax
+
+
+def test_cell_order_far_field_is_used_and_agrees_with_creation_order(nb, oracle):
+    """N = 65536 (BASELINE config 3 size): sorted and unsorted runs are two different summation orders of the
+    same pair terms -- far-field tiles drop a clamp that is provably the identity -- so they must agree far
+    inside the tolerance; the sorted run must actually take the far-field form for most tiles."""
+    n = 65536
+    b = oracle.init_bodies(n)
+    gs = make(nb, b)            # default at this size: cell order
+    gu = make(nb, b, sort=-1)
+    assert gs.describe()["cell_order"] is True and gu.describe()["cell_order"] is False
+    assert gu.far_fraction() == 0.0
+    assert gs.far_fraction() > 0.5
+    fs, fu = gs.forces(), gu.forces()
+    scale = max(np.abs(fu[0]).max(), np.abs(fu[1]).max())
+    assert np.abs(fs[0] - fu[0]).max() <= 1e-11 * scale and np.abs(fs[1] - fu[1]).max() <= 1e-11 * scale
+    gs.step(4)
+    gu.step(4)
+    s, u = gs.fetch(), gu.fetch()
+    for k in (0, 1):
+        assert np.abs(s[k] - u[k]).max() <= 1e-12 * np.abs(u[k]).max()
+    for k in (4, 5):
+        assert np.abs(s[k] - u[k]).max() <= 1e-10 * np.abs(u[k]).max()
+    # sampled rows of the sorted run's forces against the CPU oracle (rows in the CALLER's order)
+    rows = 16
+    xf, yf = np.zeros(n), np.zeros(n)
+    for lo in (0, 31000, n - rows):
+        oracle.lib().oracle_forces_rows(n, 0, lo, lo + rows, 8, b.x, b.y, b.mass, b.radius, xf, yf)
+        sl = slice(lo, lo + rows)
+        np.testing.assert_allclose(fs[0][sl], xf[sl], rtol=1e-10, atol=1e-10 * np.abs(xf[sl]).max())
+        np.testing.assert_allclose(fs[1][sl], yf[sl], rtol=1e-10, atol=1e-10 * np.abs(yf[sl]).max())
+
+
+def test_cell_order_results_do_not_depend_on_how_steps_are_split(nb, oracle, monkeypatch):
+    """Re-sorts happen on a schedule that counts steps, also across graph launches (2 steps each)."""
+    monkeypatch.setenv("NBODY_SORT_INTERVAL", "3")
+    n = 17000
+    b = oracle.init_bodies(n)
+    b.xv *= 3.0e4    # make bodies really move between sorts (DELTA_T is 5e-6)
+    b.yv *= 3.0e4
+    runs = []
+    for split in ((8,), (1,) * 8, (2, 5, 1), (3, 3, 2), (7, 1)):
+        g = make(nb, b, sort=1)
+        assert g.describe()["sort_interval"] == 3
+        for k in split:
+            g.step(k)
+        runs.append(g.fetch())
+        assert g.describe()["sorts"] == 3, (split, g.describe())     # at init, before step 3, before step 6
+        g.close()
+    for r in runs[1:]:
+        assert bits_equal(runs[0], r)
+    g = make(nb, b, sort=1, use_graph=-1)
+    g.step(8)
+    assert bits_equal(runs[0], g.fetch())
+    ref = b.copy()
+    oracle.run(ref, 8, trig=0, threads=8)
+    np.testing.assert_allclose(runs[0][0], ref.x, rtol=POS_RTOL, atol=1e-12)
+    np.testing.assert_allclose(runs[0][5], ref.yv, rtol=VEL_RTOL, atol=1e-12)
+
+
+def test_cell_order_set_state_restarts_from_the_callers_order(nb, oracle):
+    n = 16500
+    b = oracle.init_bodies(n)
+    g = make(nb, b, sort=1)
+    g.step(3)
+    first = g.fetch()
+    g.set_state(b.x, b.y, b.xv, b.yv)
+    x, y, xf, yf, xv, yv = g.fetch()
+    assert np.array_equal(x, b.x) and np.array_equal(y, b.y) and np.array_equal(xv, b.xv) and np.array_equal(yv, b.yv)
+    assert not xf.any() and not yf.any()
+    g.step(3)
+    assert bits_equal(first, g.fetch())
+    # a different state through the same handle
+    c = first
+    g.set_state(c[0], c[1], c[4], c[5])
+    g.step(2)
+    h = nb.NBodyGPU(c[0], c[1], c[4], c[5], b.mass, b.radius, mode=nb.MODE_FAST, symmetric=1, sort=1)
+    h.step(2)
+    assert bits_equal(g.fetch(), h.fetch())
+
+
+def test_cell_order_coincident_bodies_keep_the_reference_convention(nb, oracle):
+    """Coincident bodies share a cell; the sort's tie-break is the original index, so "lower index gets
+    (+force, 0)" (atan2(0,0) = 0, nbody-seq.c:91-106) survives the permutation."""
+    n = 18000
+    b = oracle.init_bodies(n)
+    pairs = ((3, 17900), (3, 9000), (700, 701), (511, 512), (0, n - 1), (12345, 2))
+    for i, j in pairs:
+        b.x[j], b.y[j] = b.x[i], b.y[i]
+    fx, fy = make(nb, b, sort=1).forces()
+    xf, yf = np.zeros(n), np.zeros(n)
+    tol = 1e-11 * max(np.abs(fx).max(), np.abs(fy).max())
+    for i in sorted({k for p in pairs for k in p}):
+        oracle.lib().oracle_forces_rows(n, 0, i, i + 1, 1, b.x, b.y, b.mass, b.radius, xf, yf)
+        assert abs(fx[i] - xf[i]) <= tol and abs(fy[i] - yf[i]) <= tol, i
+    # the coincident partner's push is not small against that tolerance: swapping the convention would fail
+    i, j = pairs[0]
+    push = b.mass[i] * b.mass[j] * 1.1 / (b.radius[i] + b.radius[j]) ** 2
+    assert push > 100 * tol
+
+
+def test_cell_order_render_paints_lowest_original_index(nb, oracle):
+    n = 16400
+    xdim, ydim = 320, 200
+    b = oracle.init_bodies(n, xdim, ydim)
+    gs = nb.NBodyGPU(b.x, b.y, b.xv, b.yv, b.mass, b.radius, xdim=xdim, ydim=ydim, mode=nb.MODE_FAST, symmetric=1, sort=1)
+    gu = nb.NBodyGPU(b.x, b.y, b.xv, b.yv, b.mass, b.radius, xdim=xdim, ydim=ydim, mode=nb.MODE_FAST, symmetric=1, sort=-1)
+    assert np.array_equal(gs.render(xdim, ydim), gu.render(xdim, ydim))
+    ref = oracle.display(b, xdim, ydim)
+    assert np.array_equal(gs.render(xdim, ydim), ref)
+
+
+def test_cell_order_same_bits_on_1_2_4_8_gpus(nb, oracle, monkeypatch):
+    k = nb.device_count()
+    if k < 2:
+        pytest.skip("needs >= 2 GPUs")
+    monkeypatch.setenv("NBODY_SORT_INTERVAL", "2")
+    n, steps = 20000, 5
+    b = oracle.init_bodies(n)
+    b.xv *= 3.0e4
+    b.yv *= 3.0e4
+    b.x[n - 1], b.y[n - 1] = b.x[1], b.y[1]
+    def run(p, p2p=0):
+        g = make(nb, b, ngpus=p, sort=1, p2p=p2p)
+        g.step(2)
+        g.step(steps - 2)
+        out = g.fetch()
+        assert g.describe()["sorts"] == 3
+        g.close()
+        return out
+    ref = run(1)
+    for p in (2, 4, 8):
+        if p > k:
+            continue
+        for p2p in (1, -1):
+            assert bits_equal(ref, run(p, p2p)), (p, p2p)

@@ -3,7 +3,24 @@ usage: python tools/sass_loop_count.py kernels_fast.o 'forces_sym_kernelILi128EL
 import collections, re, subprocess, sys
 
 obj, pat = sys.argv[1], sys.argv[2]
-want_shfl = len(sys.argv) > 3 and sys.argv[3] == "shfl"
+want_shfl = len(sys.argv) > 3 and sys.argv[3] in ("shfl", "allshfl")
+want_all = len(sys.argv) > 3 and sys.argv[3] in ("all", "allshfl")
+
+
+def report(name, body):
+    hist = collections.Counter()
+    for _, x in body:
+        x = re.sub(r"^@!?U?P\d+\s+", "", x)
+        hist[x.split()[0].split(".")[0]] += 1
+    fp64 = sum(v for k2, v in hist.items() if k2 in ("DFMA", "DMUL", "DADD", "DSETP"))
+    mufu = hist.get("MUFU", 0)
+    other = sum(hist.values()) - fp64 - mufu
+    pairs = max(mufu, 1)
+    print(name)
+    print("  loop %d instr, %d pairs: FP64 %.2f/pair, MUFU %.2f, other %.2f  -> model %.1f issue cycles/pair" %
+          (len(body), pairs, fp64 / pairs, mufu / pairs, other / pairs, (2 * fp64 + 2 * mufu + other) / pairs))
+    print("  " + " ".join("%s:%d" % kv for kv in hist.most_common()))
+
 txt = subprocess.run(["cuobjdump", "-sass", obj], capture_output=True, text=True, check=True).stdout
 cur, funcs = None, {}
 for line in txt.splitlines():
@@ -35,18 +52,10 @@ for name, ins in funcs.items():
         nd = sum(1 for _, x in body if re.match(r"(@!?U?P\d+\s+)?DFMA", x))
         if want_shfl and not any("SHFL" in x for _, x in body):
             continue
+        if want_all and nd > 16:
+            report(name, body)
         if best is None or nd > best[0]:
             best = (nd, body)
-    nd, body = best
-    hist = collections.Counter()
-    for _, x in body:
-        x = re.sub(r"^@!?U?P\d+\s+", "", x)
-        hist[x.split()[0].split(".")[0]] += 1
-    fp64 = sum(v for k2, v in hist.items() if k2 in ("DFMA", "DMUL", "DADD", "DSETP"))
-    mufu = hist.get("MUFU", 0)
-    other = sum(hist.values()) - fp64 - mufu
-    pairs = mufu
-    print(name)
-    print("  loop %d instr, %d pairs: FP64 %.2f/pair, MUFU %.2f, other %.2f  -> model %.1f issue cycles/pair" %
-          (len(body), pairs, fp64 / pairs, mufu / pairs, other / pairs, (2 * fp64 + 2 * mufu + other) / pairs))
-    print("  " + " ".join("%s:%d" % kv for kv in hist.most_common()))
+    if want_all:
+        continue
+    report(name, best[1])
