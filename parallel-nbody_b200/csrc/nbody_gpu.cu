@@ -84,6 +84,8 @@ struct Shard {
 
 using namespace nbody;
 
+constexpr int NSTAGE_BUF = 3;   // pinned staging buffers: the three arrays of a fetch / an upload are in flight together
+
 struct nbody_gpu {
     nbody_gpu_cfg cfg;
     int n = 0;
@@ -97,8 +99,6 @@ struct nbody_gpu {
     int sort_interval = 0;       // steps between re-sorts
     long long since_sort = 0;    // steps since the last sort
     long long sorts = 0;
-    std::vector<int> orig_host;  // host copy of orig, refreshed lazily
-    bool orig_host_valid = false;
     bool p2p = false;            // sharded symmetric: exchange fused into the kernels over peer memory (no NCCL per step)
     unsigned long long epoch = 0;
     int nblocks = 0;             // symmetric: number of SYM_RB row blocks
@@ -106,7 +106,7 @@ struct nbody_gpu {
     int graph_steps = 0;         // steps captured per graph launch (even), 0 = graphs off
     bool sharded = false;
     std::vector<Shard> shards;   // local shards (1, or ngpus in single-process mode)
-    double2 *stage = nullptr;    // pinned host staging, npad elements
+    double2 *stage = nullptr;    // pinned host staging, NSTAGE_BUF x npad elements
     long long launches[4] = {0, 0, 0, 0};   // force, integrate, reduce, nccl
 };
 
@@ -364,7 +364,6 @@ static int resort(nbody_gpu *h, bool gather)
     h->launches[2] += static_cast<long long>(h->shards.size()) * 3;
     h->since_sort = 0;
     h->sorts += 1;
-    h->orig_host_valid = false;
     return NBODY_GPU_OK;
 }
 
@@ -454,16 +453,17 @@ static int run_one_step(nbody_gpu *h, StepMarks *marks)
     return NBODY_GPU_OK;
 }
 
-static int upload(nbody_gpu *h, double2 *Shard::*field, int slot, const double *a, const double *b)
+// Interleave two host arrays into pinned staging buffer `buf` and enqueue one H2D copy per local device.
+// The caller synchronises (sync_all) before the staging buffer is used again.
+static int upload(nbody_gpu *h, double2 *Shard::*field, int slot, const double *a, const double *b, int buf)
 {
-    // interleave on the host into pinned staging, then one H2D copy per local device
-    for (int i = 0; i < h->n; ++i) h->stage[i] = make_double2(a ? a[i] : 0.0, b ? b[i] : 0.0);
-    for (int i = h->n; i < h->npad; ++i) h->stage[i] = make_double2(0.0, 0.0);
+    double2 *stage = h->stage + static_cast<size_t>(buf) * h->npad;
+    for (int i = 0; i < h->n; ++i) stage[i] = make_double2(a ? a[i] : 0.0, b ? b[i] : 0.0);
+    for (int i = h->n; i < h->npad; ++i) stage[i] = make_double2(0.0, 0.0);
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
         double2 *dst = field ? s.*field : s.pos[slot];
-        NB_CUDA(cudaMemcpyAsync(dst, h->stage, sizeof(double2) * h->npad, cudaMemcpyHostToDevice, s.stream));
-        NB_CUDA(cudaStreamSynchronize(s.stream));   // staging buffer is reused
+        NB_CUDA(cudaMemcpyAsync(dst, stage, sizeof(double2) * h->npad, cudaMemcpyHostToDevice, s.stream));
     }
     return NBODY_GPU_OK;
 }
@@ -795,7 +795,7 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
             }
         }
     }
-    NB_CUDA(cudaMallocHost(&h->stage, sizeof(double2) * static_cast<size_t>(h->npad)));
+    NB_CUDA(cudaMallocHost(&h->stage, sizeof(double2) * static_cast<size_t>(h->npad) * NSTAGE_BUF));
 
     if (h->sharded) {
         const char *why = "";
@@ -815,9 +815,9 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
         }
     }
 
-    int rc = upload(h, nullptr, 0, x, y);
-    if (!rc) rc = upload(h, &Shard::mr, 0, mass, radius);
-    if (!rc) rc = upload(h, &Shard::vel, 0, xv, yv);
+    int rc = upload(h, nullptr, 0, x, y, 0);
+    if (!rc) rc = upload(h, &Shard::mr, 0, mass, radius, 1);
+    if (!rc) rc = upload(h, &Shard::vel, 0, xv, yv, 2);
     h->cur = 0;
     if (!rc && h->sorted) {
         for (Shard &s : h->shards) {
@@ -831,6 +831,7 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
         rc = setup_p2p(h);
         if (!rc && !h->p2p && cfg->p2p > 0) rc = fail(NBODY_GPU_ECUDA, "peer-memory exchange requested but peer access is unavailable");
     }
+    if (!rc) rc = sync_all(h);   // the staging buffers are free again
     return rc;
 }
 
@@ -863,8 +864,8 @@ int nbody_gpu_set_state(nbody_gpu *h, const double *x, const double *y, const do
 {
     if (!h || !x || !y || !xv || !yv) return fail(NBODY_GPU_EINVAL, "NULL argument");
     int rc = sync_all(h);
-    if (!rc) rc = upload(h, nullptr, h->cur, x, y);
-    if (!rc) rc = upload(h, &Shard::vel, 0, xv, yv);
+    if (!rc) rc = upload(h, nullptr, h->cur, x, y, 0);
+    if (!rc) rc = upload(h, &Shard::vel, 0, xv, yv, 1);
     if (rc) return rc;
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
@@ -877,10 +878,8 @@ int nbody_gpu_set_state(nbody_gpu *h, const double *x, const double *y, const do
     if (h->sorted) {
         rc = resort(h, false);
         if (rc) return rc;
-        rc = sync_all(h);   // with the fused peer exchange no device may run ahead into a step before all have sorted
-        if (rc) return rc;
     }
-    return NBODY_GPU_OK;
+    return sync_all(h);   // the staging buffers are free again; no device runs ahead into a step
 }
 
 int nbody_gpu_step(nbody_gpu *h, int steps)
@@ -996,29 +995,34 @@ int nbody_gpu_sync(nbody_gpu *h)
     return sync_all(h);
 }
 
-static int download(nbody_gpu *h, const double2 *src, cudaStream_t st, double *a, double *b)
+// Device array of shard 0 -> pinned staging buffer `buf` (asynchronous), in the caller's body order: cell order
+// is undone on the device first.  download_finish de-interleaves after the stream has been synchronised.
+static int download_begin(nbody_gpu *h, const double2 *src, int buf, bool wanted)
 {
-    if (!a && !b) return NBODY_GPU_OK;
-    NB_CUDA(cudaMemcpyAsync(h->stage, src, sizeof(double2) * static_cast<size_t>(h->n), cudaMemcpyDeviceToHost, st));
-    if (h->sorted && !h->orig_host_valid) {
-        h->orig_host.resize(static_cast<size_t>(h->n));
-        NB_CUDA(cudaMemcpyAsync(h->orig_host.data(), h->shards[0].orig, sizeof(int) * static_cast<size_t>(h->n), cudaMemcpyDeviceToHost, st));
-        h->orig_host_valid = true;
+    if (!wanted) return NBODY_GPU_OK;
+    Shard &s = h->shards[0];
+    if (h->sorted) {
+        launch_unsort(src, s.orig, s.gat[buf], h->n, s.stream);
+        src = s.gat[buf];
     }
-    NB_CUDA(cudaStreamSynchronize(st));
-    if (h->sorted) {   // slot order -> the caller's body order
-        const int *orig = h->orig_host.data();
-        for (int s = 0; s < h->n; ++s) {
-            if (a) a[orig[s]] = h->stage[s].x;
-            if (b) b[orig[s]] = h->stage[s].y;
-        }
-        return NBODY_GPU_OK;
-    }
-    for (int i = 0; i < h->n; ++i) {
-        if (a) a[i] = h->stage[i].x;
-        if (b) b[i] = h->stage[i].y;
-    }
+    NB_CUDA(cudaMemcpyAsync(h->stage + static_cast<size_t>(buf) * h->npad, src, sizeof(double2) * static_cast<size_t>(h->n),
+                            cudaMemcpyDeviceToHost, s.stream));
     return NBODY_GPU_OK;
+}
+
+static void download_finish(nbody_gpu *h, int buf, double *a, double *b)
+{
+    const double2 *stage = h->stage + static_cast<size_t>(buf) * h->npad;
+    if (a && b) {
+        for (int i = 0; i < h->n; ++i) {
+            a[i] = stage[i].x;
+            b[i] = stage[i].y;
+        }
+    } else if (a) {
+        for (int i = 0; i < h->n; ++i) a[i] = stage[i].x;
+    } else if (b) {
+        for (int i = 0; i < h->n; ++i) b[i] = stage[i].y;
+    }
 }
 
 int nbody_gpu_forces(nbody_gpu *h, double *xf, double *yf)
@@ -1045,9 +1049,11 @@ int nbody_gpu_forces(nbody_gpu *h, double *xf, double *yf)
     if (rc) return rc;
     Shard &s0 = h->shards[0];
     NB_CUDA(cudaSetDevice(s0.device));
-    rc = download(h, s0.frc, s0.stream, xf, yf);
+    rc = download_begin(h, s0.frc, 0, xf || yf);
+    if (!rc) rc = sync_all(h);
     if (rc) return rc;
-    return sync_all(h);
+    download_finish(h, 0, xf, yf);
+    return NBODY_GPU_OK;
 }
 
 int nbody_gpu_fetch(nbody_gpu *h, double *x, double *y, double *xf, double *yf, double *xv, double *yv)
@@ -1063,12 +1069,14 @@ int nbody_gpu_fetch(nbody_gpu *h, double *x, double *y, double *xf, double *yf, 
     }
     Shard &s0 = h->shards[0];
     NB_CUDA(cudaSetDevice(s0.device));
-    rc = download(h, s0.pos[h->cur], s0.stream, x, y);
-    if (!rc) rc = download(h, s0.frc, s0.stream, xf, yf);
-    if (!rc) rc = download(h, s0.vel, s0.stream, xv, yv);
+    rc = download_begin(h, s0.pos[h->cur], 0, x || y);
+    if (!rc) rc = download_begin(h, s0.frc, 1, xf || yf);
+    if (!rc) rc = download_begin(h, s0.vel, 2, xv || yv);
+    if (!rc) rc = sync_all(h);
     if (rc) return rc;
-    rc = sync_all(h);
-    if (rc) return rc;
+    download_finish(h, 0, x, y);
+    download_finish(h, 1, xf, yf);
+    download_finish(h, 2, xv, yv);
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
         NB_CUDA(cudaGetLastError());
