@@ -15,7 +15,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libnbody_gpu.so")
+LIB_PATH = os.environ.get("NBODY_GPU_LIB") or os.path.join(_HERE, "libnbody_gpu.so")   # override: A/B runs of two builds
 
 MODE_EXACT = 0
 MODE_FAST = 1
