@@ -7,7 +7,8 @@
 Workload (BASELINE.json config 4, the one `metric` is quoted on): N = 262144 bodies from the
 reference initialiser (srand(27102015), world 1024x768; reference nbody/nbody-par.c:208-222),
 fast mode, STRONG scaling: the same 262144 bodies are sharded over the GPUs (row blocks of the symmetric
-kernel) and one ncclAllGather per step replaces MPI_Allgatherv (nbody-par.c:913).
+kernel); the per-step exchange that replaces MPI_Allgatherv (nbody-par.c:913) is fused into the kernels over
+NVLink peer memory (or one ncclAllGather when the GPUs cannot map each other).
 A step = one force + integrate (+ exchange) pass.  value = K * N * (N-1) / t, t = device time of
 the K-step loop (CUDA events on the library's stream), max over ranks.
 
@@ -328,8 +329,16 @@ def main():
     if ipp and far > 0.0:
         # far-field tiles issue 17 FP64-pipe instructions per unordered pair instead of 19 (forces_sym.cuh)
         ipp = ipp * (1.0 - far) + 8.5 * far
+    # DRAM bytes of one force-kernel launch from the committed ncu --set full capture of this very configuration
+    # (profiles/r1_ncu_forces_sym_far_N262144.txt: read 32.6 MB + written 1.150 GB, the reaction partial sums);
+    # other configurations have no capture
+    traffic = None
+    if n == N_DEFAULT and world == 1 and desc.get("symmetric") and desc.get("cell_order"):
+        traffic = 32.6e6 + 1.1504e9   # bytes per launch (algorithmic: the colpart partial sums, N^2/1024*16 B = 1.07e9)
     roofline = {"bound": "fp64", "achieved": algo_tflops, "peak": peak_tf, "unit": "TFLOP/s",
-                "frac": algo_tflops / peak_tf, "traffic": None,
+                "frac": algo_tflops / peak_tf, "traffic": traffic,
+                "traffic_source": "profiles/r1_ncu_forces_sym_far_N262144.txt (dram__bytes_read.sum + dram__bytes_write.sum, "
+                                  "bytes per launch)" if traffic else None,
                 "peak_source": "measured live: nbody_gpu_fp64_peak DFMA kernel on this GPU "
                                "(MEASURED_PEAKS.json has no FP64 entry)",
                 "kernel": desc["kernel"], "evaluation": "symmetric (each unordered pair once)" if desc["symmetric"]
@@ -361,8 +370,8 @@ def main():
             "warmup": args.warmup, "ms_per_step": t_ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "BASELINE config 4: N=%d bodies, reference initialiser (srand 27102015), world %dx%d, "
-                                   "%s mode, rows sharded over %d GPU(s), all-gather of new positions per step"
-                                   % (n, XDIM, YDIM, args.mode, world),
+                                   "%s mode, row blocks sharded over %d GPU(s), per-step exchange: %s"
+                                   % (n, XDIM, YDIM, args.mode, world, desc.get("exchange", "none")),
                        "n": n, "mode": args.mode, "parallelism": "row-shard x%d" % world,
                        "l2": "256 MiB scratch overwritten between steps (L2 flush); working set per step 8 MiB"},
             "steps_per_s": args.steps / (t_ms * 1e-3),
