@@ -59,7 +59,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=N_DEFAULT)
+    ap.add_argument("--n", "--bodies", dest="n", type=int, default=N_DEFAULT)   # under torchrun use --bodies (--n is ambiguous there)
     ap.add_argument("--mode", default="fast", choices=["fast", "exact"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -298,14 +298,15 @@ def main():
     # ---- end to end through the C ABI with host buffers every step --------------------------
     e2e = None
     if not args.no_e2e:
-        x, y, xf, yf, xv, yv = g.fetch()
+        host = g.fetch()                       # the caller's six arrays, reused every step like the reference's world struct
+        x, y, xf, yf, xv, yv = host
         e_steps = max(2, min(args.steps, 5))
         barrier()
         t0 = time.perf_counter()
         for _ in range(e_steps):
             g.set_state(x, y, xv, yv)          # H2D: positions + velocities
             g.step(1)
-            x, y, xf, yf, xv, yv = g.fetch()   # D2H: the six columns the reference prints
+            g.fetch(out=host)                  # D2H: the six columns the reference prints
         barrier()
         e_dt = maxreduce(time.perf_counter() - t0)
         e2e = {"value": e_steps * pairs_per_step / e_dt, "unit": UNIT,

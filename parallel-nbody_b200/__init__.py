@@ -162,9 +162,16 @@ class NBodyGPU:
         _check(lib().nbody_gpu_forces(self._h, xf, yf))
         return xf, yf
 
-    def fetch(self):
-        """(x, y, xf, yf, xv, yv): the six columns the reference's print() shows."""
-        out = [np.empty(self.n) for _ in range(6)]
+    def fetch(self, out=None):
+        """(x, y, xf, yf, xv, yv): the six columns the reference's print() shows.  `out`: six float64 arrays of
+        length n to fill instead of allocating new ones."""
+        if out is None:
+            out = [np.empty(self.n) for _ in range(6)]
+        else:
+            out = list(out)
+            for a in out:
+                if a.dtype != np.float64 or a.shape != (self.n,) or not a.flags.c_contiguous:
+                    raise ValueError("fetch(out=...) needs six contiguous float64 arrays of length n")
         _check(lib().nbody_gpu_fetch(self._h, *[a.ctypes.data_as(ctypes.c_void_p) for a in out]))
         return tuple(out)
 

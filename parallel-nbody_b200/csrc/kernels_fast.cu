@@ -53,6 +53,7 @@ int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream
     forces_sym_kernel<__VA_ARGS__><<<grid, threads, smem, st>>>(a);
     int threads = 128;
     if (variant == 1) threads = 256;
+    if (variant == 20 || variant == 21 || variant == 22) threads = 64;
     const int smem = sym_smem_bytes(threads);
     switch (variant) {
     default: NB_SYM_LAUNCH(128, 4) break;             // near flavour 3, far flavour 5
@@ -60,6 +61,9 @@ int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream
     case 4: NB_SYM_LAUNCH(128, 4, 1, 2) break;
     case 5: NB_SYM_LAUNCH(128, 4, 1, 8) break;
     case 10: NB_SYM_LAUNCH(128, 4, 1, 4, 0, 4) break;  // round-1 pair arithmetic
+    case 20: NB_SYM_LAUNCH(64, 8, 1, 1) break;
+    case 21: NB_SYM_LAUNCH(64, 8, 1, 2) break;
+    case 22: NB_SYM_LAUNCH(64, 8, 1, 4) break;
     }
 #undef NB_SYM_LAUNCH
     return 0;
