@@ -59,6 +59,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--jsplit", type=int, default=0, help="development: number of j-chunks (0 = library default)")
     ap.add_argument("--n", "--bodies", dest="n", type=int, default=N_DEFAULT)   # under torchrun use --bodies (--n is ambiguous there)
     ap.add_argument("--mode", default="fast", choices=["fast", "exact"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
@@ -260,7 +261,7 @@ def main():
     mode = nb.MODE_FAST if args.mode == "fast" else nb.MODE_EXACT
     b = oracle_lib.init_bodies(n, XDIM, YDIM)      # the reference's initial state (synthetic)
     g = nb.NBodyGPU(b.x, b.y, b.xv, b.yv, b.mass, b.radius, xdim=XDIM, ydim=YDIM, mode=mode,
-                    device=local_rank, rank=rank, nranks=world, nccl_id=nccl_id)
+                    device=local_rank, rank=rank, nranks=world, nccl_id=nccl_id, jsplit=args.jsplit)
 
     def barrier():
         if dist is not None:

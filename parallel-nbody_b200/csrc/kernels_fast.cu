@@ -44,7 +44,12 @@ void launch_integrate_fast(const IntegrateArgs &a, cudaStream_t st)
 int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream_t st)
 {
     if (nblocks_here <= 0) return 0;
-    static const int variant = getenv("NBODY_SYM_VARIANT") ? atoi(getenv("NBODY_SYM_VARIANT")) : 0;
+    // development knob: NBODY_SYM_VARIANT pins a tuning variant; default: 8 bodies per thread (2 warps per CTA) for
+    // large worlds, where halving the per-step LDS/SHFL/address work wins 2.7 %, 4 bodies per thread below
+    // (more, shorter CTAs: better tail at N = 65536).  A function of n only, like every other choice that
+    // affects the summation order.
+    static const int env_variant = getenv("NBODY_SYM_VARIANT") ? atoi(getenv("NBODY_SYM_VARIANT")) : 0;
+    const int variant = env_variant ? env_variant : (a.n >= SYM_WIDE_N ? 22 : 0);
     dim3 grid(nblocks_here, nsplit);
     cudaError_t e;
 #define NB_SYM_LAUNCH(...)                                                                                          \
@@ -56,14 +61,14 @@ int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream
     if (variant == 20 || variant == 21 || variant == 22) threads = 64;
     const int smem = sym_smem_bytes(threads);
     switch (variant) {
-    default: NB_SYM_LAUNCH(128, 4) break;             // near flavour 3, far flavour 5
+    default: NB_SYM_LAUNCH(128, 4) break;             // near flavour 3, far flavour 5; default for n < SYM_WIDE_N
     case 1: NB_SYM_LAUNCH(256, 2) break;
     case 4: NB_SYM_LAUNCH(128, 4, 1, 2) break;
     case 5: NB_SYM_LAUNCH(128, 4, 1, 8) break;
     case 10: NB_SYM_LAUNCH(128, 4, 1, 4, 0, 4) break;  // round-1 pair arithmetic
     case 20: NB_SYM_LAUNCH(64, 8, 1, 1) break;
     case 21: NB_SYM_LAUNCH(64, 8, 1, 2) break;
-    case 22: NB_SYM_LAUNCH(64, 8, 1, 4) break;
+    case 22: NB_SYM_LAUNCH(64, 8, 1, 4) break;         // default for n >= SYM_WIDE_N
     }
 #undef NB_SYM_LAUNCH
     return 0;

@@ -148,7 +148,7 @@ static void choose_split_sym(int n, int requested, int *nsplit, int *chunk)
 {
     int c;
     if (requested > 0) c = (n + requested - 1) / requested;
-    else c = n / 64;
+    else c = n / 128;   // 128 chunks: shorter CTAs, less tail on an 8-way shard (+1 % on one GPU at N = 262144)
     if (c < 2048) c = 2048;
     c = (c + SYM_RB - 1) / SYM_RB * SYM_RB;
     *chunk = c;
@@ -1088,7 +1088,7 @@ int nbody_gpu_describe(const nbody_gpu *h, char *buf, int len)
 {
     if (!h) return 0;
     const bool fast = h->cfg.mode == NBODY_GPU_MODE_FAST;
-    const char *kernel = !fast ? "forces_kernel<EXACT>" : h->symmetric ? "forces_sym_kernel<128,4>" : "forces_fast_kernel<2,4,1,true>";
+    const char *kernel = !fast ? "forces_kernel<EXACT>" : h->symmetric ? (h->n >= SYM_WIDE_N ? "forces_sym_kernel<64,8>" : "forces_sym_kernel<128,4>") : "forces_fast_kernel<2,4,1,true>";
     // FP64-pipe instructions per directed pair-interaction (SASS counts): the symmetric
     // kernel issues 19 per unordered pair = 2 interactions; exact mode is not a fixed count (divisions, branches)
     // (19 near, 17 in far-field tiles: see nbody_gpu_far_fraction)
