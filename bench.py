@@ -304,15 +304,26 @@ def main():
         e_steps = max(2, min(args.steps, 5))
         barrier()
         t0 = time.perf_counter()
+        split = [0.0, 0.0, 0.0]
         for _ in range(e_steps):
+            ta = time.perf_counter()
             g.set_state(x, y, xv, yv)          # H2D: positions + velocities
+            tb = time.perf_counter()
             g.step(1)
+            g.sync()
+            tc = time.perf_counter()
             g.fetch(out=host)                  # D2H: the six columns the reference prints
+            td = time.perf_counter()
+            split[0] += tb - ta
+            split[1] += tc - tb
+            split[2] += td - tc
         barrier()
         e_dt = maxreduce(time.perf_counter() - t0)
         e2e = {"value": e_steps * pairs_per_step / e_dt, "unit": UNIT,
                "h2d_bytes_per_step": 4 * 8 * n, "d2h_bytes_per_step": 6 * 8 * n, "steps": e_steps,
-               "call": "nbody_gpu_set_state + nbody_gpu_step(1) + nbody_gpu_fetch per step, wall clock"}
+               "call": "nbody_gpu_set_state + nbody_gpu_step(1) + nbody_gpu_fetch per step, wall clock",
+               "rank0_ms_per_step": {"set_state": 1e3 * split[0] / e_steps, "step": 1e3 * split[1] / e_steps,
+                                     "fetch": 1e3 * split[2] / e_steps}}
 
     if rank != 0:
         g.close()
