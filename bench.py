@@ -92,9 +92,10 @@ class ClockSampler:
 
     def _pump(self):
         for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+            self.lines.append((time.perf_counter(), ln.strip()))
 
-    def stop(self):
+    def stop(self, t0=None, t1=None):
+        """Summary of the samples taken between t0 and t1 (perf_counter; all samples if none fall inside)."""
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -104,7 +105,8 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons, pw = [], [], set(), []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        inside = [ln for (ts, ln) in self.lines if t0 is not None and t0 <= ts <= t1 + 0.15]
+        for ln in (inside or [ln for (_, ln) in self.lines]):
             f = [t.strip() for t in ln.split(",")]
             if len(f) < 8:
                 continue
@@ -261,7 +263,8 @@ def main():
     mode = nb.MODE_FAST if args.mode == "fast" else nb.MODE_EXACT
     b = oracle_lib.init_bodies(n, XDIM, YDIM)      # the reference's initial state (synthetic)
     g = nb.NBodyGPU(b.x, b.y, b.xv, b.yv, b.mass, b.radius, xdim=XDIM, ydim=YDIM, mode=mode,
-                    device=local_rank, rank=rank, nranks=world, nccl_id=nccl_id, jsplit=args.jsplit)
+                    device=local_rank, rank=rank, nranks=world, nccl_id=nccl_id, jsplit=args.jsplit,
+                    p2p=int(os.environ.get("NBODY_BENCH_P2P", "0")))   # development: -1 = NCCL exchange
 
     def barrier():
         if dist is not None:
@@ -279,15 +282,21 @@ def main():
 
     # ---- device-resident timed region ------------------------------------------------------
     g.step(args.warmup)
+    g.step_profiled(1, flush_l2=True)   # one more untimed step on the timed path: its scratch buffer exists afterwards
     g.sync()
     l0 = sum(g.launch_count()[1][:3])   # our kernels only (force, integrate, reduce), not NCCL's
+    # the sampler (a fork of nvidia-smi: tens of ms on an 8-GPU box) starts BEFORE the barrier, so that rank 0 does
+    # not enter the timed region late and leave the other ranks waiting for it in their first exchange
     sampler = ClockSampler(local_rank)
-    barrier()
     if rank == 0:
         sampler.start()
-    prof = g.step_profiled(args.steps, flush_l2=True)
+        time.sleep(0.3)
     barrier()
-    clocks = sampler.stop() if rank == 0 else None
+    t_region0 = time.perf_counter()
+    prof = g.step_profiled(args.steps, flush_l2=True)
+    t_region1 = time.perf_counter()
+    barrier()
+    clocks = sampler.stop(t_region0, t_region1) if rank == 0 else None
     launches = sum(g.launch_count()[1][:3]) - l0
     t_ms = maxreduce(prof["total"])
     force_ms = maxreduce(prof["force"])

@@ -70,6 +70,7 @@ struct Shard {
     void *sort_tmp = nullptr;
     size_t sort_tmp_bytes = 0;
     double2 *gat[4] = {nullptr, nullptr, nullptr, nullptr};   // gather targets of a re-sort; scratch for unsorting
+    void *flush = nullptr;       // 256 MiB L2-flush scratch of nbody_gpu_step_profiled, kept between calls
     int v0 = 0, nv = SYM_V;      // virtual ranks owned by this shard
     PeerTable peers = {};        // fused peer-memory exchange (npeers = 0: not in use)
     unsigned long long *flags = nullptr;   // [2][MAX_PEERS] epoch words written by the peers
@@ -173,6 +174,7 @@ static void free_shard(Shard &s)
     if (s.frc) cudaFree(s.frc);
     if (s.part) cudaFree(s.part);
     if (s.colpart) cudaFree(s.colpart);
+    if (s.flush) cudaFree(s.flush);
     if (s.orig) cudaFree(s.orig);
     if (s.boxes) cudaFree(s.boxes);
     if (s.mr0) cudaFree(s.mr0);
@@ -947,19 +949,18 @@ int nbody_gpu_step_profiled(nbody_gpu *h, int steps, int flush_l2, float out_ms[
     const size_t flush_bytes = 256u << 20;
     const size_t nsh = h->shards.size();
     EventMarks marks(h, steps);
-    std::vector<void *> scratch(nsh, nullptr);
     for (size_t k = 0; k < nsh; ++k) {
         NB_CUDA(cudaSetDevice(h->shards[k].device));
         for (int st = 0; st < steps; ++st)
             for (int ph = 0; ph < 6; ++ph) NB_CUDA(cudaEventCreate(&marks.at(k, st, ph)));
-        if (flush_l2) NB_CUDA(cudaMalloc(&scratch[k], flush_bytes));
+        if (flush_l2 && !h->shards[k].flush) NB_CUDA(cudaMalloc(&h->shards[k].flush, flush_bytes));   // first call only
         NB_CUDA(cudaEventRecord(h->shards[k].ev0, h->shards[k].stream));
     }
     for (int st = 0; st < steps; ++st) {
         if (flush_l2) {
             for (size_t k = 0; k < nsh; ++k) {
                 NB_CUDA(cudaSetDevice(h->shards[k].device));
-                NB_CUDA(cudaMemsetAsync(scratch[k], st & 0xff, flush_bytes, h->shards[k].stream));
+                NB_CUDA(cudaMemsetAsync(h->shards[k].flush, st & 0xff, flush_bytes, h->shards[k].stream));
             }
         }
         marks.step = st;
@@ -976,6 +977,14 @@ int nbody_gpu_step_profiled(nbody_gpu *h, int steps, int flush_l2, float out_ms[
         NB_CUDA(cudaEventSynchronize(s.ev1));
         float acc[4] = {0.f, 0.f, 0.f, 0.f}, t = 0.f;
         NB_CUDA(cudaEventElapsedTime(&acc[0], s.ev0, s.ev1));
+        if (getenv("NBODY_PROFILE_SPLIT")) {   // development knob: per-step phase times of this shard
+            for (int st = 0; st < steps; ++st) {
+                float ph_ms[5];
+                for (int ph = 0; ph < 5; ++ph) NB_CUDA(cudaEventElapsedTime(&ph_ms[ph], marks.at(k, st, ph), marks.at(k, st, ph + 1)));
+                fprintf(stderr, "[nbody_gpu] shard %d step %d: force %.3f fold %.3f exchA %.3f integrate %.3f exchB %.3f ms\n",
+                        s.part_index, st, ph_ms[0], ph_ms[1], ph_ms[2], ph_ms[3], ph_ms[4]);
+            }
+        }
         for (int st = 0; st < steps; ++st) {
             // phases: 0-1 force kernel | 1-2 symmetric fold | 2-3 exchange A | 3-4 integrate | 4-5 exchange B
             static const int bucket[5] = {1, 2, 3, 2, 3};
@@ -989,7 +998,6 @@ int nbody_gpu_step_profiled(nbody_gpu *h, int steps, int flush_l2, float out_ms[
             if (acc[q] > out_ms[q]) out_ms[q] = acc[q];
         for (int st = 0; st < steps; ++st)
             for (int ph = 0; ph < 6; ++ph) cudaEventDestroy(marks.at(k, st, ph));
-        if (scratch[k]) cudaFree(scratch[k]);
         NB_CUDA(cudaGetLastError());
     }
     return NBODY_GPU_OK;

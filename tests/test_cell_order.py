@@ -174,3 +174,35 @@ def test_cell_order_same_bits_on_1_2_4_8_gpus(nb, oracle, monkeypatch):
             continue
         for p2p in (1, -1):
             assert bits_equal(ref, run(p, p2p)), (p, p2p)
+
+
+def test_wide_kernel_same_bits_across_gpu_counts(nb, oracle):
+    """N >= 131072 runs the 64 x 8 shape of the symmetric kernel (2 warps per CTA, 8 bodies per thread) with
+    max(1024, N/256)-body j-chunks: still a function of N only, so 1, 2, 4 and 8 GPUs give the same bits; and the
+    result stays within tolerance of the directed kernel (an independent summation structure)."""
+    n, steps = 131072 + 300, 2
+    b = oracle.init_bodies(n)
+    g = make(nb, b)
+    assert g.describe()["kernel"] == "forces_sym_kernel<64,8>"
+    g.step(steps)
+    ref = g.fetch()
+    g.close()
+    d = nb.NBodyGPU(b.x, b.y, b.xv, b.yv, b.mass, b.radius, mode=nb.MODE_FAST, symmetric=-1)
+    d.step(steps)
+    dd = d.fetch()
+    d.close()
+    for k in (0, 1):
+        assert np.abs(ref[k] - dd[k]).max() <= 1e-12 * np.abs(dd[k]).max()
+    for k in (4, 5):
+        assert np.abs(ref[k] - dd[k]).max() <= 1e-10 * np.abs(dd[k]).max()
+    fs = max(np.abs(dd[2]).max(), np.abs(dd[3]).max())
+    assert np.abs(ref[2] - dd[2]).max() <= 1e-8 * fs and np.abs(ref[3] - dd[3]).max() <= 1e-8 * fs
+    k = nb.device_count()
+    for p in (2, 4, 8):
+        if p > k:
+            continue
+        for p2p in (1, -1):
+            h = make(nb, b, ngpus=p, p2p=p2p)
+            h.step(steps)
+            assert bits_equal(ref, h.fetch()), (p, p2p)
+            h.close()
