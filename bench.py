@@ -352,14 +352,14 @@ def main():
         # far-field tiles issue 17 FP64-pipe instructions per unordered pair instead of 19 (forces_sym.cuh)
         ipp = ipp * (1.0 - far) + 8.5 * far
     # DRAM bytes of one force-kernel launch from the committed ncu --set full capture of this very configuration
-    # (profiles/r1_ncu_forces_sym_far_N262144.txt: read 32.6 MB + written 1.150 GB, the reaction partial sums);
+    # (profiles/r1_ncu_forces_sym_wide_N262144.txt: read 32.6 MB + written 1.150 GB, the reaction partial sums);
     # other configurations have no capture
     traffic = None
     if n == N_DEFAULT and world == 1 and desc.get("symmetric") and desc.get("cell_order"):
-        traffic = 32.6e6 + 1.1504e9   # bytes per launch (algorithmic: the colpart partial sums, N^2/1024*16 B = 1.07e9)
+        traffic = 24.6e6 + 1.5534e9   # bytes per launch (algorithmic: colpart N^2/1024*16 B = 1.07e9 + rowpart N*128*16 B = 0.54e9)
     roofline = {"bound": "fp64", "achieved": algo_tflops, "peak": peak_tf, "unit": "TFLOP/s",
                 "frac": algo_tflops / peak_tf, "traffic": traffic,
-                "traffic_source": "profiles/r1_ncu_forces_sym_far_N262144.txt (dram__bytes_read.sum + dram__bytes_write.sum, "
+                "traffic_source": "profiles/r1_ncu_forces_sym_wide_N262144.txt (dram__bytes_read.sum + dram__bytes_write.sum, "
                                   "bytes per launch)" if traffic else None,
                 "peak_source": "measured live: nbody_gpu_fp64_peak DFMA kernel on this GPU "
                                "(MEASURED_PEAKS.json has no FP64 entry)",
