@@ -352,7 +352,7 @@ def main():
         # far-field tiles issue 17 FP64-pipe instructions per unordered pair instead of 19 (forces_sym.cuh)
         ipp = ipp * (1.0 - far) + 8.5 * far
     # DRAM bytes of one force-kernel launch from the committed ncu --set full capture of this very configuration
-    # (profiles/r1_ncu_forces_sym_wide_N262144.txt: read 32.6 MB + written 1.150 GB, the reaction partial sums);
+    # (profiles/r1_ncu_forces_sym_wide_N262144.txt: read 24.6 MB + written 1.553 GB: the reaction and row partial sums);
     # other configurations have no capture
     traffic = None
     if n == N_DEFAULT and world == 1 and desc.get("symmetric") and desc.get("cell_order"):
