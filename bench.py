@@ -45,7 +45,7 @@ if os.environ.get("NCCL_DEBUG", "").upper().startswith("V"):
 os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))   # oracle_lib (cpu_baseline leg and --impl reference only)
 
 METRIC = "fp64_pair_interactions_per_s"
 UNIT = "pair-interactions/s"
@@ -243,7 +243,6 @@ def main():
 
     import torch
     import pnb200
-    import oracle_lib   # body initialiser + cpu_baseline leg only; never on the measured GPU path
     nb = pnb200.load()
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback")
@@ -261,8 +260,9 @@ def main():
 
     n = args.n
     mode = nb.MODE_FAST if args.mode == "fast" else nb.MODE_EXACT
-    b = oracle_lib.init_bodies(n, XDIM, YDIM)      # the reference's initial state (synthetic)
-    g = nb.NBodyGPU(b.x, b.y, b.xv, b.yv, b.mass, b.radius, xdim=XDIM, ydim=YDIM, mode=mode,
+    # the reference's synthetic initial state (nbody-par.c:208-222) from the library's own host helper
+    bx, by, bxv, byv, bmass, bradius = nb.reference_init(n, XDIM, YDIM)
+    g = nb.NBodyGPU(bx, by, bxv, byv, bmass, bradius, xdim=XDIM, ydim=YDIM, mode=mode,
                     device=local_rank, rank=rank, nranks=world, nccl_id=nccl_id, jsplit=args.jsplit,
                     p2p=int(os.environ.get("NBODY_BENCH_P2P", "0")))   # development: -1 = NCCL exchange
 
@@ -374,6 +374,8 @@ def main():
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
+        import oracle_lib   # the checker, timed as the CPU baseline: the only place this arm touches oracle/
+        b = oracle_lib.init_bodies(n, XDIM, YDIM)
         threads = os.cpu_count() or 1
         v, rws, dt = cpu_sample(oracle_lib, b, n, threads, args.cpu_seconds)
         v1, rws1, dt1 = cpu_seq_sample(oracle_lib, b, n, min(6.0, args.cpu_seconds / 2))

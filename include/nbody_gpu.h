@@ -148,6 +148,13 @@ void nbody_gpu_partition(int n, int nranks, int rank, int *lo, int *hi);
  * counts n/P, ranks 1..n%P get one more; displacements are the prefix sum. */
 void nbody_gpu_partition_reference(int n, int nranks, int *counts, int *displs);
 
+/* The reference's synthetic initial state (initialize_simulation_data, nbody-par.c:208-222; nbody-seq.c:440-449):
+ * srand(27102015), four rand() draws per body (x, y, xv, yv), radius and mass from the body index.  Host code
+ * only (the C library's rand() sequence is part of parity); b*b and n*n are formed in double so that n > 46340
+ * is defined.  For harnesses (bench.py) that need the reference's workload without the reference. */
+void nbody_gpu_reference_init(int n, int xdim, int ydim, double *x, double *y, double *xv, double *yv,
+                              double *mass, double *radius);
+
 /* ncclGetUniqueId through the library's NCCL binding; out = NBODY_GPU_NCCL_ID_BYTES bytes. */
 int nbody_gpu_nccl_unique_id(void *out);
 

@@ -76,6 +76,8 @@ def lib():
     L.nbody_gpu_partition.restype = None
     L.nbody_gpu_partition_reference.argtypes = [ci, ci, ctypes.POINTER(ci), ctypes.POINTER(ci)]
     L.nbody_gpu_partition_reference.restype = None
+    L.nbody_gpu_reference_init.argtypes = [ci, ci, ci] + [_dp] * 6
+    L.nbody_gpu_reference_init.restype = None
     L.nbody_gpu_nccl_unique_id.argtypes = [ctypes.c_char_p]
     L.nbody_gpu_device_count.restype = ci
     L.nbody_gpu_fp64_peak.argtypes = [ci, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
@@ -110,6 +112,13 @@ def partition_reference(n, nranks):
     displs = (ctypes.c_int * nranks)()
     lib().nbody_gpu_partition_reference(n, nranks, counts, displs)
     return list(counts), list(displs)
+
+
+def reference_init(n, xdim=1024, ydim=768):
+    """The reference's synthetic initial state (nbody-par.c:208-222): (x, y, xv, yv, mass, radius)."""
+    out = [np.empty(n) for _ in range(6)]
+    lib().nbody_gpu_reference_init(n, xdim, ydim, *out)
+    return tuple(out)
 
 
 def fp64_peak(device=-1, ms_budget=200):

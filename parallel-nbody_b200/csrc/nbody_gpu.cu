@@ -7,6 +7,7 @@
 // There is no CPU fallback: every entry point that computes needs a CUDA device.
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -692,6 +693,25 @@ void nbody_gpu_partition_reference(int n, int nranks, int *counts, int *displs)
     for (int r = n % nranks; r > 0; --r) counts[r] += 1;
     displs[0] = 0;
     for (int r = 1; r < nranks; ++r) displs[r] = displs[r - 1] + counts[r - 1];
+}
+
+void nbody_gpu_reference_init(int n, int xdim, int ydim, double *x, double *y, double *xv, double *yv, double *mass,
+                              double *radius)
+{
+    // nbody-par.c:208-222 / nbody-seq.c:440-449 with the reference's seed (nbody-seq.c:26): four rand() draws per
+    // body in the order X, Y, XV, YV; b*b and n*n formed in double (int in the reference: the same for n <= 46340,
+    // undefined behaviour above)
+    if (n < 1 || xdim < 1 || ydim < 1 || !x || !y || !xv || !yv || !mass || !radius) return;
+    srand(27102015);
+    const double diag = sqrt(1.0 * ((xdim * xdim) + (ydim * ydim)));
+    for (int b = 0; b < n; ++b) {
+        x[b] = (rand() % xdim);
+        y[b] = (rand() % ydim);
+        radius[b] = 1 + ((static_cast<double>(b) * b + 1.0) * diag) / (25.0 * (static_cast<double>(n) * n + 1.0));
+        mass[b] = radius[b] * radius[b] * radius[b];
+        xv[b] = ((rand() % 20000) - 10000) / 2000.0;
+        yv[b] = ((rand() % 20000) - 10000) / 2000.0;
+    }
 }
 
 int nbody_gpu_nccl_unique_id(void *out)

@@ -90,3 +90,13 @@ def test_product_sources_do_not_reference_the_oracle():
                     if re.search(r"#\s*include[^\n]*oracle|liboracle|oracle_[a-z_]+\s*\(|import\s+oracle|-loracle", txt):
                         bad.append(os.path.join(dp, f))
     assert not bad, bad
+
+
+@pytest.mark.parametrize("n", [1, 32, 128, 4096, 50000])
+def test_library_initialiser_is_the_reference_one(nb, oracle, n):
+    """nbody_gpu_reference_init (host helper used by bench.py) against the oracle's restatement of
+    nbody-par.c:208-222, which tests/test_oracle.py pins to the reference program's own output."""
+    got = nb.reference_init(n)
+    want = oracle.init_bodies(n)
+    for a, f in zip(got, ("x", "y", "xv", "yv", "mass", "radius")):
+        assert np.array_equal(a.view(np.uint64), getattr(want, f).view(np.uint64)), f
