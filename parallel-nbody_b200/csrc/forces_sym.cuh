@@ -182,7 +182,10 @@ __device__ __noinline__ double sym_col_rescan(const double2 *pos, const double2 
     return c;
 }
 
-template <int SYM_THREADS, int SYM_IB, int MINB = 1, int UNROLL = 4, int FLAVOR = 3, int FAR_FLAVOR = 5>
+// PERSIST: instead of one CTA per (row block, j-chunk) the grid is one wave of CTAs that pull items from a counter,
+// largest chunks first, so no SM idles while the last full-size CTAs of a launch finish (an 8-way shard has only
+// ~14 waves).  An item is computed by exactly the same code whichever CTA takes it: the bits do not change.
+template <int SYM_THREADS, int SYM_IB, int MINB = 1, int UNROLL = 4, int FLAVOR = 3, int FAR_FLAVOR = 5, bool PERSIST = false>
 __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const SymArgs a)
 {
     static_assert(SYM_RB == SYM_THREADS * SYM_IB, "row block = threads x bodies per thread");
@@ -194,23 +197,40 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     double *s_box = reinterpret_cast<double *>(s_col + SYM_WARPS * TILE_J);   // [STAGES][SYM_BOX_DOUBLES] tile boxes
     double *s_bbox = s_box + STAGES * SYM_BOX_DOUBLES;                        // [SYM_BOX_DOUBLES] this row block's box
     uint64_t *s_full = reinterpret_cast<uint64_t *>(s_bbox + SYM_BOX_DOUBLES);
-    int *s_flag = reinterpret_cast<int *>(s_full + STAGES);                 // [2]
+    int *s_flag = reinterpret_cast<int *>(s_full + STAGES);                 // [2] coincidence flags, [2] = work item
 
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int warp = tid >> 5;
-    const int blk = sym_owned_block(blockIdx.x, a.v0, a.nv);               // row block index
-    const int i0 = blk * SYM_RB;
-    const int i1 = min(a.n, i0 + SYM_RB);
-    const int jc0 = blockIdx.y * a.chunk;
-    const int j1 = min(a.n, jc0 + a.chunk);
-    const int j0 = max(jc0, i0);            // tiles below the block are not ours (tile aligned: chunk % SYM_RB == 0)
-    if (i0 >= a.n || j0 >= j1) return;      // block beyond the last body, or whole chunk below the block
-    const int ntiles = (j1 - j0 + TILE_J - 1) / TILE_J;
-
     if (tid == 0) {
         for (int s = 0; s < STAGES; ++s) mbar_init(&s_full[s], 1);
         mbar_init_fence();
+    }
+    uint32_t gt = 0;   // tiles this CTA has consumed so far: stage and mbarrier parity carry over from item to item
+    for (;;) {
+    int bx = blockIdx.x, by = blockIdx.y;   // (high chunks first was tried for the plain launch: 0.5 % slower)
+    if (PERSIST) {
+        __syncthreads();   // the previous item is finished by every thread
+        if (tid == 0) s_flag[2] = atomicAdd(a.counter, 1);
+        __syncthreads();
+        const int item = s_flag[2];
+        if (item >= a.nitems) break;
+        bx = item % a.nblocks_here;
+        by = a.nsplit - 1 - item / a.nblocks_here;   // high chunks first: every block has a full chunk there
+    }
+    const int blk = sym_owned_block(bx, a.v0, a.nv);               // row block index
+    const int i0 = blk * SYM_RB;
+    const int i1 = min(a.n, i0 + SYM_RB);
+    const int jc0 = by * a.chunk;
+    const int j1 = min(a.n, jc0 + a.chunk);
+    const int j0 = max(jc0, i0);            // tiles below the block are not ours (tile aligned: chunk % SYM_RB == 0)
+    if (i0 >= a.n || j0 >= j1) {            // block beyond the last body, or whole chunk below the block
+        if (PERSIST) continue;
+        return;
+    }
+    const int ntiles = (j1 - j0 + TILE_J - 1) / TILE_J;
+
+    if (tid == 0) {
         s_flag[0] = 0;
         s_flag[1] = 0;
     }
@@ -232,7 +252,7 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     __syncthreads();
 
     auto issue = [&](int tile) {
-        const int st = tile % STAGES;
+        const int st = (gt + tile) % STAGES;
         const int jb = j0 + tile * TILE_J;
         const uint32_t bytes = static_cast<uint32_t>(min(TILE_J, j1 - jb)) * sizeof(double2);
         const uint32_t box_bytes = a.boxes ? SYM_BOX_DOUBLES * 8 : 0;
@@ -261,8 +281,8 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     }
 
     for (int tile = 0; tile < ntiles; ++tile) {
-        const int st = tile % STAGES;
-        mbar_wait(&s_full[st], (tile / STAGES) & 1);
+        const int st = (gt + tile) % STAGES;
+        mbar_wait(&s_full[st], ((gt + tile) / STAGES) & 1);
         const int jb = j0 + tile * TILE_J;
         const int cnt = min(TILE_J, j1 - jb);
         const double2 *tp = s_pos + st * TILE_J;
@@ -355,8 +375,11 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     for (int k = 0; k < SYM_IB; ++k) {
         if (idx[k] < a.n) {
             const double gm = NB_GRAVITY * b[k].m;
-            a.rowpart[static_cast<size_t>(blockIdx.y) * a.npad + idx[k]] = make_double2(gm * b[k].ax, gm * b[k].ay);
+            a.rowpart[static_cast<size_t>(by) * a.npad + idx[k]] = make_double2(gm * b[k].ax, gm * b[k].ay);
         }
+    }
+    gt += static_cast<uint32_t>(ntiles);
+    if (!PERSIST) break;
     }
 }
 

@@ -41,9 +41,12 @@ void launch_integrate_fast(const IntegrateArgs &a, cudaStream_t st)
     integrate_kernel<MODE_FAST><<<(rows + 127) / 128, 128, 0, st>>>(a);
 }
 
-int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream_t st)
+int launch_forces_sym(SymArgs a, int nblocks_here, int nsplit, cudaStream_t st)
 {
     if (nblocks_here <= 0) return 0;
+    a.nblocks_here = nblocks_here;
+    a.nsplit = nsplit;
+    a.nitems = nblocks_here * nsplit;
     // development knob: NBODY_SYM_VARIANT pins a tuning variant; default: 8 bodies per thread (2 warps per CTA) for
     // large worlds, where halving the per-step LDS/SHFL/address work wins 2.7 %, 4 bodies per thread below
     // (more, shorter CTAs: better tail at N = 65536).  A function of n only, like every other choice that
@@ -58,8 +61,22 @@ int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream
     forces_sym_kernel<__VA_ARGS__><<<grid, threads, smem, st>>>(a);
     int threads = 128;
     if (variant == 1) threads = 256;
-    if (variant == 20 || variant == 21 || variant == 22) threads = 64;
+    if (variant == 20 || variant == 21 || variant == 22 || variant == 30) threads = 64;
     const int smem = sym_smem_bytes(threads);
+    // persistent variants: one wave of CTAs (as many as are resident at once) pulling items from a.counter
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+#define NB_SYM_LAUNCH_P(CTAS_PER_SM, ...)                                                                           \
+    if (!a.counter) return static_cast<int>(cudaErrorInvalidValue);                                                 \
+    e = cudaFuncSetAttribute(forces_sym_kernel<__VA_ARGS__>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);    \
+    if (e != cudaSuccess) return static_cast<int>(e);                                                              \
+    e = cudaMemsetAsync(a.counter, 0, sizeof(int), st);                                                             \
+    if (e != cudaSuccess) return static_cast<int>(e);                                                              \
+    forces_sym_kernel<__VA_ARGS__><<<min(a.nitems, sms * CTAS_PER_SM), threads, smem, st>>>(a);
     switch (variant) {
     default: NB_SYM_LAUNCH(128, 4) break;             // near flavour 3, far flavour 5; default for n < SYM_WIDE_N
     case 1: NB_SYM_LAUNCH(256, 2) break;
@@ -69,8 +86,12 @@ int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream
     case 20: NB_SYM_LAUNCH(64, 8, 1, 1) break;
     case 21: NB_SYM_LAUNCH(64, 8, 1, 2) break;
     case 22: NB_SYM_LAUNCH(64, 8, 1, 4) break;         // default for n >= SYM_WIDE_N
+    case 23: NB_SYM_LAUNCH(128, 4) break;              // the 128 x 4 shape at any n
+    case 30: NB_SYM_LAUNCH_P(4, 64, 8, 1, 4, 3, 5, true) break;
+    case 31: NB_SYM_LAUNCH_P(2, 128, 4, 1, 4, 3, 5, true) break;
     }
 #undef NB_SYM_LAUNCH
+#undef NB_SYM_LAUNCH_P
     return 0;
 }
 

@@ -71,6 +71,7 @@ struct Shard {
     void *sort_tmp = nullptr;
     size_t sort_tmp_bytes = 0;
     double2 *gat[4] = {nullptr, nullptr, nullptr, nullptr};   // gather targets of a re-sort; scratch for unsorting
+    int *sym_counter = nullptr;  // work-item counter of the persistent symmetric kernel
     void *flush = nullptr;       // 256 MiB L2-flush scratch of nbody_gpu_step_profiled, kept between calls
     int v0 = 0, nv = SYM_V;      // virtual ranks owned by this shard
     PeerTable peers = {};        // fused peer-memory exchange (npeers = 0: not in use)
@@ -175,6 +176,7 @@ static void free_shard(Shard &s)
     if (s.frc) cudaFree(s.frc);
     if (s.part) cudaFree(s.part);
     if (s.colpart) cudaFree(s.colpart);
+    if (s.sym_counter) cudaFree(s.sym_counter);
     if (s.flush) cudaFree(s.flush);
     if (s.orig) cudaFree(s.orig);
     if (s.boxes) cudaFree(s.boxes);
@@ -260,6 +262,7 @@ static void enqueue_forces(nbody_gpu *h, Shard &s, int slot)
         a.rowpart = s.part;
         a.colpart = s.colpart;
         a.boxes = s.boxes;
+        a.counter = s.sym_counter;
         a.n = h->n;
         a.npad = h->npad;
         a.chunk = h->chunk;
@@ -804,6 +807,7 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
                 s.nblocks_owned = static_cast<int>(slots);
                 NB_CUDA(cudaMalloc(&s.colpart, bytes * slots));
                 NB_CUDA(cudaMemsetAsync(s.colpart, 0, bytes * slots, s.stream));
+                NB_CUDA(cudaMalloc(&s.sym_counter, sizeof(int)));
                 NB_CUDA(cudaMalloc(&s.vbuf, bytes * SYM_V));
                 NB_CUDA(cudaMemsetAsync(s.vbuf, 0, bytes * SYM_V, s.stream));
             }

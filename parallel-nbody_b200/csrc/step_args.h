@@ -36,6 +36,9 @@ struct SymArgs {
     int npad;
     int chunk;            // j-chunk length, a multiple of SYM_RB
     int v0, nv;           // this device owns the row blocks B with (B % SYM_V) in [v0, v0+nv): "virtual ranks"
+    int *counter;         // persistent launch: work-item counter, zeroed before every launch (else nullptr)
+    int nitems;           // persistent launch: nblocks_here * nsplit
+    int nblocks_here, nsplit;
 };
 
 // The symmetric kernel's partial sums are combined through SYM_V fixed "virtual ranks": row block B
@@ -133,7 +136,7 @@ void launch_integrate_exact(const IntegrateArgs &a, cudaStream_t st);
 void launch_forces_fast(const ForceArgs &a, int nsplit, cudaStream_t st);
 void launch_integrate_fast(const IntegrateArgs &a, cudaStream_t st);
 void launch_reduce_fast(const IntegrateArgs &a, cudaStream_t st);
-int launch_forces_sym(const SymArgs &a, int nblocks_here, int nsplit, cudaStream_t st);   // returns cudaError_t
+int launch_forces_sym(SymArgs a, int nblocks_here, int nsplit, cudaStream_t st);   // returns cudaError_t
 void launch_render(const double2 *pos, const double2 *mr, int n, int xdim, int ydim, int *owner, unsigned char *rgb,
                    cudaStream_t st);
 void launch_sym_reduce(const SymReduceArgs &a, cudaStream_t st);
