@@ -155,6 +155,10 @@ void nbody_gpu_partition_reference(int n, int nranks, int *counts, int *displs);
 void nbody_gpu_reference_init(int n, int xdim, int ydim, double *x, double *y, double *xv, double *yv,
                               double *mass, double *radius);
 
+/* The cell-order sort key of a position (host mirror of the device code): Hilbert index, 16 bits per axis, of
+ * the cell (x, y) * 65535 / max(xdim, ydim).  The device sorts by (this key, original index).  Host only. */
+unsigned nbody_gpu_cell_key(double x, double y, int xdim, int ydim);
+
 /* ncclGetUniqueId through the library's NCCL binding; out = NBODY_GPU_NCCL_ID_BYTES bytes. */
 int nbody_gpu_nccl_unique_id(void *out);
 

@@ -76,6 +76,8 @@ def lib():
     L.nbody_gpu_partition.restype = None
     L.nbody_gpu_partition_reference.argtypes = [ci, ci, ctypes.POINTER(ci), ctypes.POINTER(ci)]
     L.nbody_gpu_partition_reference.restype = None
+    L.nbody_gpu_cell_key.argtypes = [ctypes.c_double, ctypes.c_double, ci, ci]
+    L.nbody_gpu_cell_key.restype = ctypes.c_uint
     L.nbody_gpu_reference_init.argtypes = [ci, ci, ci] + [_dp] * 6
     L.nbody_gpu_reference_init.restype = None
     L.nbody_gpu_nccl_unique_id.argtypes = [ctypes.c_char_p]
@@ -119,6 +121,11 @@ def reference_init(n, xdim=1024, ydim=768):
     out = [np.empty(n) for _ in range(6)]
     lib().nbody_gpu_reference_init(n, xdim, ydim, *out)
     return tuple(out)
+
+
+def cell_key(x, y, xdim=1024, ydim=768):
+    """Hilbert cell index the device sorts positions by (host mirror)."""
+    return int(lib().nbody_gpu_cell_key(float(x), float(y), xdim, ydim))
 
 
 def fp64_peak(device=-1, ms_budget=200):

@@ -22,7 +22,7 @@
 
 namespace nbody {
 
-__device__ __forceinline__ unsigned hilbert_index16(unsigned x, unsigned y)
+__host__ __device__ __forceinline__ unsigned hilbert_index16(unsigned x, unsigned y)
 {
     constexpr unsigned N = 1u << 16;
     unsigned d = 0;
@@ -115,6 +115,14 @@ __global__ void __launch_bounds__(TILE_J) tile_boxes_kernel(const double2 *pos, 
         }
         boxes[static_cast<size_t>(blockIdx.x) * SYM_BOX_DOUBLES + q] = r;
     }
+}
+
+// Host mirror of sort_keys_kernel's key (without the original-index tie-break), for tests of the curve itself.
+unsigned cell_key_host(double x, double y, double scale)
+{
+    const double cx = fmin(fmax(x * scale, 0.0), 65535.0);
+    const double cy = fmin(fmax(y * scale, 0.0), 65535.0);
+    return hilbert_index16(static_cast<unsigned>(cx), static_cast<unsigned>(cy));
 }
 
 size_t sort_temp_bytes(int n)

@@ -717,6 +717,12 @@ void nbody_gpu_reference_init(int n, int xdim, int ydim, double *x, double *y, d
     }
 }
 
+unsigned nbody_gpu_cell_key(double x, double y, int xdim, int ydim)
+{
+    if (xdim < 1 || ydim < 1) return 0;
+    return cell_key_host(x, y, 65535.0 / static_cast<double>(xdim > ydim ? xdim : ydim));
+}
+
 int nbody_gpu_nccl_unique_id(void *out)
 {
     if (!out) return fail(NBODY_GPU_EINVAL, "out is NULL");

@@ -124,6 +124,7 @@ struct PermuteArgs {
     int n;
 };
 size_t sort_temp_bytes(int n);
+unsigned cell_key_host(double x, double y, double scale);
 int launch_sort(const SortArgs &a, cudaStream_t st);   // returns cudaError_t
 void launch_permute(const PermuteArgs &a, cudaStream_t st);
 void launch_unsort(const double2 *in, const int *orig, double2 *out, int n, cudaStream_t st);

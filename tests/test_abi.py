@@ -100,3 +100,29 @@ def test_library_initialiser_is_the_reference_one(nb, oracle, n):
     want = oracle.init_bodies(n)
     for a, f in zip(got, ("x", "y", "xv", "yv", "mass", "radius")):
         assert np.array_equal(a.view(np.uint64), getattr(want, f).view(np.uint64)), f
+
+
+def test_cell_key_is_a_hilbert_curve(nb):
+    """The sort key of the cell order: a bijection of the 65536 x 65536 cells onto 32 bits whose consecutive
+    indices are edge-neighbouring cells (checked on the cells of a 64 x 64 pixel world, which the scale maps to a
+    1024-cell stride, and on unit cells of a 65535-pixel world), monotone in nothing else; out-of-range and NaN
+    positions clamp instead of wrapping."""
+    side = 65535
+    cells = {}
+    for cx in range(40):
+        for cy in range(40):
+            k = nb.cell_key(cx, cy, side, side)          # scale 1: pixel = cell
+            assert k not in cells
+            cells[k] = (cx, cy)
+    keys = sorted(cells)
+    steps = [abs(cells[a][0] - cells[b][0]) + abs(cells[a][1] - cells[b][1]) for a, b in zip(keys, keys[1:]) if b == a + 1]
+    assert steps and all(s == 1 for s in steps)          # consecutive indices = neighbouring cells
+    # an aligned 2^k x 2^k square of cells occupies one contiguous index range (locality of the curve)
+    sq = sorted(k for k, (cx, cy) in cells.items() if cx < 32 and cy < 32)
+    assert sq[-1] - sq[0] == 32 * 32 - 1
+    assert nb.cell_key(-5.0, 3.0, side, side) == nb.cell_key(0.0, 3.0, side, side)
+    assert nb.cell_key(1e9, 3.0, side, side) == nb.cell_key(65535.0, 3.0, side, side)
+    assert nb.cell_key(float("nan"), 0.0, side, side) == nb.cell_key(0.0, 0.0, side, side)
+    # the reference world: 1024 x 768 pixels map to 64 cells per pixel; a sub-cell move keeps the key
+    assert nb.cell_key(100.0, 100.0) == nb.cell_key(100.001, 100.001)
+    assert nb.cell_key(100.0, 100.0) != nb.cell_key(101.0, 100.0)
