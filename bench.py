@@ -83,7 +83,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "25"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._pump, daemon=True)
             self.t.start()
@@ -287,16 +287,28 @@ def main():
     l0 = sum(g.launch_count()[1][:3])   # our kernels only (force, integrate, reduce), not NCCL's
     # the sampler (a fork of nvidia-smi: tens of ms on an 8-GPU box) starts BEFORE the barrier, so that rank 0 does
     # not enter the timed region late and leave the other ranks waiting for it in their first exchange
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
-        time.sleep(0.3)
+    sampler = ClockSampler(local_rank)   # every rank records its own GPU
+    sampler.start()
+    time.sleep(0.3)
     barrier()
     t_region0 = time.perf_counter()
     prof = g.step_profiled(args.steps, flush_l2=True)
     t_region1 = time.perf_counter()
     barrier()
-    clocks = sampler.stop(t_region0, t_region1) if rank == 0 else None
+    clocks = sampler.stop(t_region0, t_region1)
+    if dist is not None:
+        # per-rank clock record: [median SM MHz, max W, samples, throttled?] of every GPU, gathered on all ranks
+        mine = torch.tensor([float(clocks.get("sm_mhz") or -1.0), float(clocks.get("power_w_max") or -1.0),
+                             float(clocks.get("samples") or 0), float(len(clocks.get("reasons") or []))],
+                            dtype=torch.float64, device="cuda")
+        allc = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allc, mine)
+        per_rank = [[float(v) for v in t.cpu().tolist()] for t in allc]
+        clocks["per_rank_sm_mhz"] = [r[0] for r in per_rank]
+        clocks["per_rank_power_w_max"] = [r[1] for r in per_rank]
+        clocks["per_rank_samples"] = [int(r[2]) for r in per_rank]
+        if any(r[3] > 0 for r in per_rank) and not clocks.get("reasons"):
+            clocks["reasons"] = ["see other ranks"]
     launches = sum(g.launch_count()[1][:3]) - l0
     t_ms = maxreduce(prof["total"])
     force_ms = maxreduce(prof["force"])
