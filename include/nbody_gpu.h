@@ -15,17 +15,22 @@
  * the message.  There is no CPU fallback anywhere behind this interface: without
  * a CUDA device nbody_gpu_init fails.
  *
+ * After a CUDA or NCCL failure inside a step, an upload or a fetch the device state is undefined: the
+ * handle remembers the first such failure and every later call on it returns that error.
+ *
  * Threading: one host thread drives a handle (the reference's step loop has one
  * caller thread per rank).  nbody_gpu_step only enqueues; fetch/sync wait.
  */
 #ifndef NBODY_GPU_H
 #define NBODY_GPU_H
 
+#include <stddef.h>
+
 #ifdef __cplusplus
 extern "C" {
 #endif
 
-#define NBODY_GPU_ABI_VERSION 2
+#define NBODY_GPU_ABI_VERSION 3
 
 enum {
     NBODY_GPU_OK = 0,
@@ -70,6 +75,8 @@ typedef struct nbody_gpu_cfg {
     int sort;       /* symmetric fast mode: 0 = library default (device arrays kept in cell order for n >= 16384 so that
                        most tiles take the far-field form of the pair; invisible to the caller: every entry point
                        speaks the caller's body order), 1 = always, -1 = keep creation order */
+    int sort_interval; /* cell order: steps between re-sorts (0 = library default, 256).  Part of what fixes the summation
+                       order: same value, same bits -- however nbody_gpu_step calls are split and on any GPU count */
 } nbody_gpu_cfg;
 
 /* Replaces calloc(world) + initialize_simulation_data + MPI_Bcast
@@ -81,7 +88,10 @@ int nbody_gpu_init(nbody_gpu **out, const nbody_gpu_cfg *cfg,
                    const double *mass, const double *radius);
 
 /* Re-upload positions and velocities into an existing handle (same n); forces are
- * zeroed.  For harnesses that time many runs without re-creating graphs. */
+ * zeroed.  For harnesses that time many runs without re-creating graphs.  One host-to-device copy per
+ * array straight from the caller's memory; returns when the copies have left the host buffers.  In
+ * multi-rank mode every rank passes the full arrays (as after the reference's MPI_Bcast, nbody-par.c:874);
+ * with the peer-memory exchange each rank uploads only its own rows and stores them into every GPU. */
 int nbody_gpu_set_state(nbody_gpu *h, const double *x, const double *y,
                         const double *xv, const double *yv);
 
@@ -93,8 +103,8 @@ int nbody_gpu_step(nbody_gpu *h, int steps);
  * synchronised; *ms receives the device time (max over this handle's devices). */
 int nbody_gpu_step_timed(nbody_gpu *h, int steps, float *ms);
 
-/* As nbody_gpu_step_timed with plain launches and a CUDA event between the phases of every
- * step: out_ms[0] = whole span, [1] = sum of force-kernel spans, [2] = integrate kernels,
+/* As nbody_gpu_step_timed with plain launches (no CUDA graph, no single-launch loop) and a CUDA event
+ * between the phases of every step: out_ms[0] = whole span, [1] = sum of force-kernel spans, [2] = integrate kernels,
  * [3] = position exchange (0 when not sharded); each the max over this handle's devices.
  * flush_l2 != 0 overwrites a 256 MiB scratch buffer between steps (inside the whole span,
  * outside the per-phase spans) so that no step starts with the previous step's L2 contents.
@@ -102,7 +112,8 @@ int nbody_gpu_step_timed(nbody_gpu *h, int steps, float *ms);
 int nbody_gpu_step_profiled(nbody_gpu *h, int steps, int flush_l2, float out_ms[4]);
 
 /* compute_forces only (clear_forces + compute_forces, nbody-seq.c:458-459) on the
- * current positions; state is otherwise untouched.  Synchronous. */
+ * current positions, into xf/yf; the handle's state -- including the last step's forces that
+ * nbody_gpu_fetch returns -- is untouched.  Synchronous. */
 int nbody_gpu_forces(nbody_gpu *h, double *xf, double *yf);
 
 /* Replaces reading world->bodies after the loop (print(), nbody-seq.c:356-365):
@@ -126,6 +137,12 @@ int nbody_gpu_far_fraction(nbody_gpu *h, double *fraction);
 
 int nbody_gpu_sync(nbody_gpu *h);
 void nbody_gpu_destroy(nbody_gpu *h);
+
+/* Page-lock a host buffer the caller keeps for the whole run (the reference's `struct world`, allocated once:
+ * nbody-par.c:810) so that nbody_gpu_set_state / nbody_gpu_fetch / nbody_gpu_init copy to and from it at full
+ * PCIe speed; without it the copies still work (the driver stages pageable memory).  Unpin before freeing. */
+int nbody_gpu_pin_host(void *ptr, size_t bytes);
+int nbody_gpu_unpin_host(void *ptr);
 
 /* Thread-local message of the last failure on this thread ("" if none). */
 const char *nbody_gpu_last_error(void);

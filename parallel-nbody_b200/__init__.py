@@ -33,7 +33,7 @@ class _Cfg(ctypes.Structure):
                 ("mode", ctypes.c_int), ("ngpus", ctypes.c_int), ("device", ctypes.c_int),
                 ("rank", ctypes.c_int), ("nranks", ctypes.c_int), ("nccl_id", ctypes.c_void_p),
                 ("jsplit", ctypes.c_int), ("use_graph", ctypes.c_int), ("symmetric", ctypes.c_int), ("p2p", ctypes.c_int),
-                ("sort", ctypes.c_int)]
+                ("sort", ctypes.c_int), ("sort_interval", ctypes.c_int)]
 
 
 _lib = None
@@ -84,6 +84,8 @@ def lib():
     L.nbody_gpu_device_count.restype = ci
     L.nbody_gpu_fp64_peak.argtypes = [ci, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
     L.nbody_gpu_abi_version.restype = ci
+    L.nbody_gpu_pin_host.argtypes = [vp, ctypes.c_size_t]
+    L.nbody_gpu_unpin_host.argtypes = [vp]
     _lib = L
     return L
 
@@ -135,6 +137,15 @@ def fp64_peak(device=-1, ms_budget=200):
     return tf.value, mhz.value
 
 
+def pin_host(a):
+    """Page-lock a numpy array the caller keeps for the whole run (set_state / fetch then copy at full PCIe speed)."""
+    _check(lib().nbody_gpu_pin_host(a.ctypes.data_as(ctypes.c_void_p), a.nbytes))
+
+
+def unpin_host(a):
+    _check(lib().nbody_gpu_unpin_host(a.ctypes.data_as(ctypes.c_void_p)))
+
+
 def _f64(a):
     return np.ascontiguousarray(a, dtype=np.float64)
 
@@ -143,7 +154,8 @@ class NBodyGPU:
     """One N-body world on the GPU(s). Arrays are host numpy float64 of length n."""
 
     def __init__(self, x, y, xv, yv, mass, radius, xdim=1024, ydim=768, mode=MODE_EXACT,
-                 ngpus=1, device=-1, rank=0, nranks=1, nccl_id=None, jsplit=0, use_graph=0, symmetric=0, p2p=0, sort=0):
+                 ngpus=1, device=-1, rank=0, nranks=1, nccl_id=None, jsplit=0, use_graph=0, symmetric=0, p2p=0, sort=0,
+                 sort_interval=0):
         x, y, xv, yv, mass, radius = map(_f64, (x, y, xv, yv, mass, radius))
         self.n = int(x.shape[0])
         for a in (y, xv, yv, mass, radius):
@@ -151,7 +163,7 @@ class NBodyGPU:
                 raise ValueError("all body arrays must have the same length")
         self._id = ctypes.create_string_buffer(nccl_id, NCCL_ID_BYTES) if nccl_id else None
         cfg = _Cfg(self.n, xdim, ydim, mode, ngpus, device, rank, nranks,
-                   ctypes.cast(self._id, ctypes.c_void_p) if self._id else None, jsplit, use_graph, symmetric, p2p, sort)
+                   ctypes.cast(self._id, ctypes.c_void_p) if self._id else None, jsplit, use_graph, symmetric, p2p, sort, sort_interval)
         self._h = ctypes.c_void_p()
         _check(lib().nbody_gpu_init(ctypes.byref(self._h), ctypes.byref(cfg), x, y, xv, yv, mass, radius))
 

@@ -40,8 +40,10 @@ struct FastBody {
     int minhi;        // min over j of the high word of dsqr: 0 <=> some dsqr == 0
 };
 
+// `self` = 1 for the pair (i, i): it adds exactly 0 like any coincident pair but must not raise the coincidence
+// word (every body would otherwise take the re-scan once per step); 0 (a literal) everywhere else.
 template <bool IMAX>
-__device__ __forceinline__ void pair_fast2(FastBody &b, double xj, double yj, double mj, double rj)
+__device__ __forceinline__ void pair_fast2(FastBody &b, double xj, double yj, double mj, double rj, int self = 0)
 {
     const double dx = xj - b.x;
     const double dy = yj - b.y;
@@ -55,7 +57,7 @@ __device__ __forceinline__ void pair_fast2(FastBody &b, double xj, double yj, do
     } else {
         forced = fmax(dsqr, mindsqr);
     }
-    b.minhi = min(b.minhi, __double2hiint(dsqr));
+    b.minhi = min(b.minhi, __double2hiint(dsqr) | self);
     const double f2 = forced * forced;
     const double q = fma(f2, dsqr, 1e-290);
     const double y0 = rsqrt_seed(q);
@@ -138,16 +140,29 @@ __global__ void __launch_bounds__(FORCE_THREADS, MINB) forces_fast_kernel(const 
         mbar_wait(&s_full[st], (tile / STAGES) & 1);
         const int jb = j0 + tile * TILE_J;
         const int cnt = min(TILE_J, j1 - jb);
-#pragma unroll UNROLL
-        for (int jj = 0; jj < cnt; ++jj) {
-            const double2 pj = s_pos[st][jj];
-            const double2 qj = s_mr[st][jj];
+        bool self_tile = false;   // does this tile hold one of the thread's own bodies?
 #pragma unroll
-            for (int k = 0; k < IB; ++k) pair_fast2<IMAX>(b[k], pj.x, pj.y, qj.x, qj.y);
+        for (int k = 0; k < IB; ++k) self_tile |= (idx[k] >= jb && idx[k] < jb + cnt);
+        if (!self_tile) {
+#pragma unroll UNROLL
+            for (int jj = 0; jj < cnt; ++jj) {
+                const double2 pj = s_pos[st][jj];
+                const double2 qj = s_mr[st][jj];
+#pragma unroll
+                for (int k = 0; k < IB; ++k) pair_fast2<IMAX>(b[k], pj.x, pj.y, qj.x, qj.y);
+            }
+        } else {
+#pragma unroll 2
+            for (int jj = 0; jj < cnt; ++jj) {
+                const double2 pj = s_pos[st][jj];
+                const double2 qj = s_mr[st][jj];
+#pragma unroll
+                for (int k = 0; k < IB; ++k) pair_fast2<IMAX>(b[k], pj.x, pj.y, qj.x, qj.y, (jb + jj == idx[k]) ? 1 : 0);
+            }
         }
 #pragma unroll
         for (int k = 0; k < IB; ++k) {
-            if (b[k].minhi == 0) {   // a coincident body (or body i itself) was in this tile
+            if (b[k].minhi == 0) {   // a body coincident with body i (not i itself) was in this tile
                 b[k].ax += coincident_rescan(&s_pos[st][0], &s_mr[st][0], cnt, jb, idx[k], b[k].x, b[k].y, b[k].r);
                 b[k].minhi = 0x7fffffff;
             }

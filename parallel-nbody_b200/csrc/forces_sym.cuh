@@ -80,8 +80,10 @@ __device__ __forceinline__ void pair_sym(SymBody &b, double xj, double yj, doubl
     ry = fma(zj, dy, ry);
 }
 
-// Directed evaluation (diagonal tiles), same arithmetic as forces_fast.cuh.
-__device__ __forceinline__ void pair_dir(SymBody &b, double xj, double yj, double mj, double rj)
+// Directed evaluation (diagonal tiles), same arithmetic as forces_fast.cuh.  `self` = 1 for the pair (i, i): its
+// dsqr = 0 adds exactly 0 like any coincident pair, but it must not raise the coincidence word (every body would
+// otherwise take the re-scan once per step).
+__device__ __forceinline__ void pair_dir(SymBody &b, double xj, double yj, double mj, double rj, int self)
 {
     const double dx = xj - b.x;
     const double dy = yj - b.y;
@@ -89,7 +91,7 @@ __device__ __forceinline__ void pair_dir(SymBody &b, double xj, double yj, doubl
     const double mindist = b.r + rj;
     const double mindsqr = mindist * mindist;
     const double forced = __longlong_as_double(max(__double_as_longlong(dsqr), __double_as_longlong(mindsqr)));
-    b.minhi = min(b.minhi, __double2hiint(dsqr));
+    b.minhi = min(b.minhi, __double2hiint(dsqr) | self);
     const double f2 = forced * forced;
     const double q = fma(f2, dsqr, 1e-290);
     const double y0 = rsqrt_seed(q);
@@ -182,10 +184,7 @@ __device__ __noinline__ double sym_col_rescan(const double2 *pos, const double2 
     return c;
 }
 
-// PERSIST: instead of one CTA per (row block, j-chunk) the grid is one wave of CTAs that pull items from a counter,
-// largest chunks first, so no SM idles while the last full-size CTAs of a launch finish (an 8-way shard has only
-// ~14 waves).  An item is computed by exactly the same code whichever CTA takes it: the bits do not change.
-template <int SYM_THREADS, int SYM_IB, int MINB = 1, int UNROLL = 4, int FLAVOR = 3, int FAR_FLAVOR = 5, bool PERSIST = false>
+template <int SYM_THREADS, int SYM_IB, int MINB = 1, int UNROLL = 4, int FLAVOR = 3, int FAR_FLAVOR = 5>
 __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const SymArgs a)
 {
     static_assert(SYM_RB == SYM_THREADS * SYM_IB, "row block = threads x bodies per thread");
@@ -197,40 +196,25 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     double *s_box = reinterpret_cast<double *>(s_col + SYM_WARPS * TILE_J);   // [STAGES][SYM_BOX_DOUBLES] tile boxes
     double *s_bbox = s_box + STAGES * SYM_BOX_DOUBLES;                        // [SYM_BOX_DOUBLES] this row block's box
     uint64_t *s_full = reinterpret_cast<uint64_t *>(s_bbox + SYM_BOX_DOUBLES);
-    int *s_flag = reinterpret_cast<int *>(s_full + STAGES);                 // [2] coincidence flags, [2] = work item
+    int *s_flag = reinterpret_cast<int *>(s_full + STAGES);                 // [2] coincidence flags
 
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int warp = tid >> 5;
-    if (tid == 0) {
-        for (int s = 0; s < STAGES; ++s) mbar_init(&s_full[s], 1);
-        mbar_init_fence();
-    }
-    uint32_t gt = 0;   // tiles this CTA has consumed so far: stage and mbarrier parity carry over from item to item
-    for (;;) {
-    int bx = blockIdx.x, by = blockIdx.y;   // (high chunks first was tried for the plain launch: 0.5 % slower)
-    if (PERSIST) {
-        __syncthreads();   // the previous item is finished by every thread
-        if (tid == 0) s_flag[2] = atomicAdd(a.counter, 1);
-        __syncthreads();
-        const int item = s_flag[2];
-        if (item >= a.nitems) break;
-        bx = item % a.nblocks_here;
-        by = a.nsplit - 1 - item / a.nblocks_here;   // high chunks first: every block has a full chunk there
-    }
+    // grid = (owned row blocks, chunks): CTAs are dispatched chunk by chunk, the short chunks (ChunkMap) last
+    const int bx = blockIdx.x, by = blockIdx.y;
     const int blk = sym_owned_block(bx, a.v0, a.nv);               // row block index
     const int i0 = blk * SYM_RB;
     const int i1 = min(a.n, i0 + SYM_RB);
-    const int jc0 = by * a.chunk;
-    const int j1 = min(a.n, jc0 + a.chunk);
-    const int j0 = max(jc0, i0);            // tiles below the block are not ours (tile aligned: chunk % SYM_RB == 0)
-    if (i0 >= a.n || j0 >= j1) {            // block beyond the last body, or whole chunk below the block
-        if (PERSIST) continue;
-        return;
-    }
+    const int jc0 = chunk_start(a.cm, by);
+    const int j1 = min(a.n, jc0 + chunk_len(a.cm, by));
+    const int j0 = max(jc0, i0);            // tiles below the block are not ours (tile aligned: chunks and blocks are)
+    if (i0 >= a.n || j0 >= j1) return;      // block beyond the last body, or whole chunk below the block
     const int ntiles = (j1 - j0 + TILE_J - 1) / TILE_J;
 
     if (tid == 0) {
+        for (int s = 0; s < STAGES; ++s) mbar_init(&s_full[s], 1);
+        mbar_init_fence();
         s_flag[0] = 0;
         s_flag[1] = 0;
     }
@@ -252,7 +236,7 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     __syncthreads();
 
     auto issue = [&](int tile) {
-        const int st = (gt + tile) % STAGES;
+        const int st = tile % STAGES;
         const int jb = j0 + tile * TILE_J;
         const uint32_t bytes = static_cast<uint32_t>(min(TILE_J, j1 - jb)) * sizeof(double2);
         const uint32_t box_bytes = a.boxes ? SYM_BOX_DOUBLES * 8 : 0;
@@ -281,8 +265,8 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     }
 
     for (int tile = 0; tile < ntiles; ++tile) {
-        const int st = (gt + tile) % STAGES;
-        mbar_wait(&s_full[st], ((gt + tile) / STAGES) & 1);
+        const int st = tile % STAGES;
+        mbar_wait(&s_full[st], (tile / STAGES) & 1);
         const int jb = j0 + tile * TILE_J;
         const int cnt = min(TILE_J, j1 - jb);
         const double2 *tp = s_pos + st * TILE_J;
@@ -295,7 +279,7 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
                 const double2 pj = tp[jj];
                 const double2 qj = tm[jj];
 #pragma unroll
-                for (int k = 0; k < SYM_IB; ++k) pair_dir(b[k], pj.x, pj.y, qj.x, qj.y);
+                for (int k = 0; k < SYM_IB; ++k) pair_dir(b[k], pj.x, pj.y, qj.x, qj.y, (jb + jj == idx[k]) ? 1 : 0);
             }
 #pragma unroll
             for (int k = 0; k < SYM_IB; ++k) {
@@ -378,9 +362,6 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
             a.rowpart[static_cast<size_t>(by) * a.npad + idx[k]] = make_double2(gm * b[k].ax, gm * b[k].ay);
         }
     }
-    gt += static_cast<uint32_t>(ntiles);
-    if (!PERSIST) break;
-    }
 }
 
 // vbuf[v][j] for the virtual ranks this device owns, one thread per (j, v).
@@ -403,7 +384,7 @@ __global__ void __launch_bounds__(128) sym_reduce_kernel(const SymReduceArgs a)
         }
     }
     if (sym_vrank(blk) == v) {                // j's own row sums, chunk ascending
-        for (int s = (blk * SYM_RB) / a.chunk; s < a.nsplit; ++s) {
+        for (int s = chunk_of(a.cm, blk * SYM_RB); s < a.cm.nsplit; ++s) {
             const double2 t = a.rowpart[static_cast<size_t>(s) * a.npad + j];
             xf += t.x;
             yf += t.y;

@@ -6,22 +6,57 @@
 #include "step_kernels.cuh"
 #include "forces_exact_wide.cuh"
 #include "render.cuh"
+#include "smalln.cuh"
 
 namespace nbody {
 
-void launch_forces_exact(const ForceArgs &a, cudaStream_t st)
+int launch_forces_exact(const ForceArgs &a, cudaStream_t st)
 {
     const int rows = a.hi - a.lo;
-    if (rows <= 0) return;
+    if (rows <= 0) return 0;
+#ifdef NBODY_DEV
     // development knob: NBODY_EXACT_VARIANT=1 selects the one-thread-per-body kernel (same bits)
     static const int variant = getenv("NBODY_EXACT_VARIANT") ? atoi(getenv("NBODY_EXACT_VARIANT")) : 0;
     if (variant == 1) {
         dim3 grid((rows + FORCE_THREADS - 1) / FORCE_THREADS, 1);
         forces_kernel<MODE_EXACT><<<grid, FORCE_THREADS, 0, st>>>(a);
-        return;
+        return 0;
     }
-    cudaFuncSetAttribute(forces_exact_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EXW_SMEM_BYTES);
+#endif
+    static bool attr_set_dev[64] = {};   // the attribute is per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    bool &attr_set = attr_set_dev[dev & 63];
+    if (!attr_set) {
+        const cudaError_t e = cudaFuncSetAttribute(forces_exact_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EXW_SMEM_BYTES);
+        if (e != cudaSuccess) return static_cast<int>(e);
+        attr_set = true;
+    }
     forces_exact_wide_kernel<<<(rows + EXW_ROWS - 1) / EXW_ROWS, EXW_THREADS, EXW_SMEM_BYTES, st>>>(a);
+    return 0;
+}
+
+int launch_small_world(const SmallArgs &a, cudaStream_t st)
+{
+    if (a.n < 1 || a.n > SMALL_N_MAX) return static_cast<int>(cudaErrorInvalidValue);
+    const size_t smem = small_smem_bytes(a.n);
+    cudaError_t e = cudaFuncSetAttribute(small_world_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return static_cast<int>(e);
+    const unsigned c = static_cast<unsigned>(small_cluster_size(a.n));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(c);
+    cfg.blockDim = dim3(SMALL_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = c;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    e = cudaLaunchKernelEx(&cfg, small_world_kernel, a);
+    return static_cast<int>(e);
 }
 
 void launch_integrate_exact(const IntegrateArgs &a, cudaStream_t st)

@@ -11,6 +11,12 @@
 //   permute_kernel     gathers pos / mr / vel / frc / orig through the sorted values
 //   tile_boxes_kernel  per TILE_J bodies: x/y range and largest radius (every step: positions move)
 //   unsort_kernel      out[orig[s]] = in[s]
+//   gather_planar_kernel   up to three double2 arrays in slot order -> planar x[] / y[] arrays in the caller's
+//                          body order (what nbody_gpu_fetch copies to the host, one copy per array)
+//   scatter_kernel     planar (a[], b[]) uploaded by nbody_gpu_set_state -> double2 rows, on this device or,
+//                      with the peer-mapped exchange, on every device (each rank uploads only its own rows)
+//   publish_kernel     a device's rows of the sharded velocity / force arrays -> every peer (before a fetch or
+//                      a re-sort of a peer-mapped job; replaces two ncclAllGather calls)
 //
 // Coincident bodies share a cell, so they stay in original-index order and the reference's convention for
 // them (lower index gets +force, nbody-seq.c:91-106) reads the same in slot order.
@@ -73,6 +79,43 @@ __global__ void __launch_bounds__(256) unsort_kernel(const double2 *in, const in
 {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s < n) out[orig[s]] = in[s];
+}
+
+__global__ void __launch_bounds__(256) gather_planar_kernel(const GatherArgs g)
+{
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= g.n) return;
+    const int o = g.orig ? g.orig[s] : s;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        if (g.src[k]) {
+            const double2 v = g.src[k][s];
+            g.a[k][o] = v.x;
+            g.b[k][o] = v.y;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) scatter_kernel(const ScatterArgs g)
+{
+    const int i = g.lo + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.hi) return;
+    const double2 v = make_double2(g.a[i], g.b[i]);
+    for (int d = 0; d < g.ndst; ++d) g.dst[d][i] = v;
+}
+
+__global__ void __launch_bounds__(256) publish_kernel(const PublishArgs g)
+{
+    const int i = g.lo + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.hi) return;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        if (g.src[k]) {
+            const double2 v = g.src[k][i];
+            for (int r = 0; r < g.npeers; ++r)
+                if (r != g.me) g.dst[k][r][i] = v;
+        }
+    }
 }
 
 __global__ void __launch_bounds__(256) iota_kernel(int *orig, int n)
@@ -154,6 +197,24 @@ void launch_unsort(const double2 *in, const int *orig, double2 *out, int n, cuda
 {
     if (n <= 0) return;
     unsort_kernel<<<(n + 255) / 256, 256, 0, st>>>(in, orig, out, n);
+}
+
+void launch_gather_planar(const GatherArgs &a, cudaStream_t st)
+{
+    if (a.n <= 0) return;
+    gather_planar_kernel<<<(a.n + 255) / 256, 256, 0, st>>>(a);
+}
+
+void launch_scatter(const ScatterArgs &a, cudaStream_t st)
+{
+    if (a.hi <= a.lo) return;
+    scatter_kernel<<<(a.hi - a.lo + 255) / 256, 256, 0, st>>>(a);
+}
+
+void launch_publish(const PublishArgs &a, cudaStream_t st)
+{
+    if (a.hi <= a.lo) return;
+    publish_kernel<<<(a.hi - a.lo + 255) / 256, 256, 0, st>>>(a);
 }
 
 void launch_iota(int *orig, int n, cudaStream_t st)

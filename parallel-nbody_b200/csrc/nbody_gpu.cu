@@ -2,8 +2,10 @@
 //
 // One handle drives either one device, several devices of one process (row shards,
 // ncclCommInitAll), or one rank of a multi-process job (row shard, ncclCommInitRank).
-// Per step and per device:  forces_kernel -> integrate_kernel -> all-gather of the new
-// positions (only when sharded).  Single-device step loops are captured in a CUDA graph.
+// Per step and per device:  force kernel [-> fold] -> exchange A -> integrate_kernel -> exchange B
+// (exchanges only when sharded: peer-memory stores + barrier kernels, or ncclAllGather).
+// Step loops are captured in CUDA graphs (one device, and sharded with the peer-memory exchange);
+// a small exact-mode world runs its whole step loop inside one kernel launch (smalln.cuh).
 // There is no CPU fallback: every entry point that computes needs a CUDA device.
 #include <cuda_runtime.h>
 
@@ -48,22 +50,41 @@ static int fail(int code, const char *fmt, ...)
                         __FILE__, __LINE__);                                                       \
     } while (0)
 
+#define NB_LAUNCH_RC(expr)                                                                         \
+    do {                                                                                           \
+        const int e_ = (expr);                                                                     \
+        if (e_ != 0)                                                                               \
+            return fail(NBODY_GPU_ECUDA, "%s failed: %s (%s:%d)", #expr,                           \
+                        cudaGetErrorString(static_cast<cudaError_t>(e_)), __FILE__, __LINE__);     \
+    } while (0)
+
+constexpr int PROF_CHUNK = 64;   // steps per pass of nbody_gpu_step_profiled (fixed event pool)
+
+// Byte offsets of the arrays other devices may address, inside one allocation per device ("arena"): one CUDA IPC
+// handle per rank maps them all, and the layout is the same on every device.
+struct ArenaLayout {
+    size_t pos[2], vel, frc, vbuf, boxes, flags, epoch, bytes;
+};
+
 struct Shard {
     int device = 0;
     int lo = 0, hi = 0;          // rows owned
     int part_index = 0;          // position of this shard in the all-gather (rank)
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_copy = nullptr;
+    unsigned char *arena = nullptr;
     double2 *pos[2] = {nullptr, nullptr};
-    double2 *mr = nullptr;
     double2 *vel = nullptr;
     double2 *frc = nullptr;
+    double2 *vbuf = nullptr;     // symmetric fast kernel: per-virtual-rank force vectors [SYM_V][npad]
+    double *boxes = nullptr;     // [ceil(n/TILE_J)][SYM_BOX_DOUBLES] per-tile bounding boxes of pos[cur]
+    unsigned long long *flags = nullptr;   // [P2P_PHASES][MAX_PEERS] barrier counts written by the peers
+    unsigned long long *epoch = nullptr;   // [P2P_PHASES] this device's own barrier counts
+    double2 *mr = nullptr;
     double2 *part = nullptr;
     double2 *colpart = nullptr;  // symmetric fast kernel: reaction partial sums [owned blocks][npad]
-    double2 *vbuf = nullptr;     // symmetric fast kernel: per-virtual-rank force vectors [SYM_V][npad]
     // cell order + far-field test of the symmetric kernel (kernels_sort.cu)
     int *orig = nullptr;         // original index of slot s (identity until the first sort)
-    double *boxes = nullptr;     // [ceil(n/TILE_J)][SYM_BOX_DOUBLES] per-tile bounding boxes, rebuilt every step
     double2 *mr0 = nullptr;      // (mass, radius) in original order, for set_state
     unsigned long long *keys[2] = {nullptr, nullptr};
     int *vals[2] = {nullptr, nullptr};
@@ -71,12 +92,15 @@ struct Shard {
     void *sort_tmp = nullptr;
     size_t sort_tmp_bytes = 0;
     double2 *gat[4] = {nullptr, nullptr, nullptr, nullptr};   // gather targets of a re-sort; scratch for unsorting
-    int *sym_counter = nullptr;  // work-item counter of the persistent symmetric kernel
+    double *plan = nullptr;      // [6][npad] planar staging: what the host sends (x y xv yv m r) / receives (x y xf yf xv yv)
+    double2 *fscratch = nullptr; // forces-only entry point: result rows (frc itself stays the last step's forces)
+    int *render_owner = nullptr; // nbody_gpu_render: per-pixel owner and the image, kept between calls
+    unsigned char *render_img = nullptr;
     void *flush = nullptr;       // 256 MiB L2-flush scratch of nbody_gpu_step_profiled, kept between calls
+    std::vector<cudaEvent_t> prof_ev;   // [PROF_CHUNK][6] phase events of nbody_gpu_step_profiled
     int v0 = 0, nv = SYM_V;      // virtual ranks owned by this shard
     PeerTable peers = {};        // fused peer-memory exchange (npeers = 0: not in use)
-    unsigned long long *flags = nullptr;   // [2][MAX_PEERS] epoch words written by the peers
-    int *p2p_err = nullptr;      // set by a wait kernel that timed out
+    int *p2p_err = nullptr;      // set by a barrier kernel that timed out
     std::vector<void *> ipc_opened;
     int nblocks_owned = 0;       // colpart slots (row blocks of the owned virtual ranks, whole groups)
     NcclComm comm = nullptr;
@@ -87,8 +111,6 @@ struct Shard {
 
 using namespace nbody;
 
-constexpr int NSTAGE_BUF = 3;   // pinned staging buffers: the three arrays of a fetch / an upload are in flight together
-
 struct nbody_gpu {
     nbody_gpu_cfg cfg;
     int n = 0;
@@ -96,21 +118,25 @@ struct nbody_gpu {
     int rows_per_shard = 0;      // ceil(n / P)
     int npad = 0;                // P * rows_per_shard (leading dimension of every array)
     int nsplit = 1;              // fast mode: j-chunks
-    int chunk = 0;               // fast mode: j-chunk length
+    int chunk = 0;               // fast mode, directed kernel: j-chunk length
+    ChunkMap cm = {};            // fast mode, symmetric kernel: j-chunks (long ones, then one-tile ones)
     bool symmetric = false;      // fast mode: evaluate each unordered pair once (forces_sym_kernel)
     bool sorted = false;         // symmetric: device arrays are kept in cell order (Shard::orig maps slots to bodies)
+    bool fused_boxes = false;    // sorted: integrate_kernel also writes the tile boxes of the new positions
+    bool small = false;          // exact mode, one device, n <= SMALL_N_MAX: the step loop is ONE launch (smalln.cuh)
     int sort_interval = 0;       // steps between re-sorts
     long long since_sort = 0;    // steps since the last sort
     long long sorts = 0;
     bool p2p = false;            // sharded symmetric: exchange fused into the kernels over peer memory (no NCCL per step)
-    unsigned long long epoch = 0;
     int nblocks = 0;             // symmetric: number of SYM_RB row blocks
     int cur = 0;                 // slot holding the current positions (the reference's world->old)
     int graph_steps = 0;         // steps captured per graph launch (even), 0 = graphs off
     bool sharded = false;
+    ArenaLayout lay = {};
     std::vector<Shard> shards;   // local shards (1, or ngpus in single-process mode)
-    double2 *stage = nullptr;    // pinned host staging, NSTAGE_BUF x npad elements
-    long long launches[4] = {0, 0, 0, 0};   // force, integrate, reduce, nccl
+    long long launches[4] = {0, 0, 0, 0};   // force, integrate, other kernels, nccl
+    int failed_rc = 0;           // a step / upload / fetch failed: the device state is undefined from then on
+    char failed_msg[512] = "";
 };
 
 namespace nbody {
@@ -127,7 +153,7 @@ static void partition(int n, int nranks, int rank, int *lo, int *hi)
     *hi = static_cast<int>(h);
 }
 
-// Fast mode: number of fixed j-chunks, a function of n only so that results do not
+// Directed fast kernel: number of fixed j-chunks, a function of n only so that results do not
 // depend on how many GPUs share the rows.
 static void choose_split(int n, int requested, int *nsplit, int *chunk)
 {
@@ -146,40 +172,72 @@ static void choose_split(int n, int requested, int *nsplit, int *chunk)
     *nsplit = (n + c - 1) / c;
 }
 
-// Symmetric kernel: chunks are multiples of SYM_RB; many small chunks keep the triangular work balanced.
-static void choose_split_sym(int n, int requested, int *nsplit, int *chunk)
+// Symmetric kernel: long chunks of max(1024, n/256) bodies (4-tile CTAs up to N = 262144: many waves per launch,
+// also on an 8-way shard) and, over the last ~n/32 bodies, one-tile chunks that are dispatched last and fill the
+// tail of the launch (ChunkMap, step_args.h).  A requested split (cfg.jsplit) gives uniform chunks.
+static ChunkMap choose_split_sym(int n, int requested)
 {
+    ChunkMap m;
     int c;
     if (requested > 0) {
         c = (n + requested - 1) / requested;
     } else {
-        // short CTAs (4 tiles up to N = 262144): more waves per launch, less tail -- +0.3 % (N = 262144) to +2.8 %
-        // (N = 65536) on one GPU against 8-tile chunks, and an 8-way shard still sees ~14 waves
         c = n / 256;
         if (c < 1024) c = 1024;
     }
     if (c < SYM_RB) c = SYM_RB;
     c = (c + SYM_RB - 1) / SYM_RB * SYM_RB;
-    *chunk = c;
-    *nsplit = (n + c - 1) / c;
+    m.chunk = c;
+    m.csmall = TILE_J;
+    if (requested > 0) {
+        m.nbig = (n + c - 1) / c;
+        m.jsmall0 = m.nbig * c;
+        m.nsplit = m.nbig;
+    } else {
+        m.nbig = (n - n / 32) / c;
+        m.jsmall0 = m.nbig * c;
+        m.nsplit = m.nbig + (n - m.jsmall0 + m.csmall - 1) / m.csmall;
+    }
+    return m;
+}
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static ArenaLayout arena_layout(int npad, bool symmetric, bool sorted, int n)
+{
+    ArenaLayout L;
+    const size_t row = sizeof(double2) * static_cast<size_t>(npad);
+    size_t at = 0;
+    auto take = [&](size_t bytes) {
+        const size_t here = at;
+        at = align_up(at + bytes, 256);
+        return here;
+    };
+    L.pos[0] = take(row);
+    L.pos[1] = take(row);
+    L.vel = take(row);
+    L.frc = take(row);
+    L.vbuf = take(symmetric ? row * SYM_V : 0);
+    L.boxes = take(sorted ? static_cast<size_t>((n + TILE_J - 1) / TILE_J) * SYM_BOX_DOUBLES * sizeof(double) : 0);
+    L.flags = take(sizeof(unsigned long long) * P2P_PHASES * MAX_PEERS);
+    L.epoch = take(sizeof(unsigned long long) * P2P_PHASES);
+    L.bytes = at;
+    return L;
 }
 
 static void free_shard(Shard &s)
 {
     cudaSetDevice(s.device);
-    for (int k = 0; k < 2; ++k) {
+    for (int k = 0; k < 2; ++k)
         if (s.graph[k]) cudaGraphExecDestroy(s.graph[k]);
-        if (s.pos[k]) cudaFree(s.pos[k]);
-    }
+    for (void *m : s.ipc_opened) cudaIpcCloseMemHandle(m);
+    s.ipc_opened.clear();
+    if (s.arena) cudaFree(s.arena);
     if (s.mr) cudaFree(s.mr);
-    if (s.vel) cudaFree(s.vel);
-    if (s.frc) cudaFree(s.frc);
     if (s.part) cudaFree(s.part);
     if (s.colpart) cudaFree(s.colpart);
-    if (s.sym_counter) cudaFree(s.sym_counter);
     if (s.flush) cudaFree(s.flush);
     if (s.orig) cudaFree(s.orig);
-    if (s.boxes) cudaFree(s.boxes);
     if (s.mr0) cudaFree(s.mr0);
     if (s.orig_tmp) cudaFree(s.orig_tmp);
     if (s.sort_tmp) cudaFree(s.sort_tmp);
@@ -189,13 +247,16 @@ static void free_shard(Shard &s)
     }
     for (int k = 0; k < 4; ++k)
         if (s.gat[k]) cudaFree(s.gat[k]);
-    for (void *m : s.ipc_opened) cudaIpcCloseMemHandle(m);
-    s.ipc_opened.clear();
-    if (s.vbuf) cudaFree(s.vbuf);
-    if (s.flags) cudaFree(s.flags);
+    if (s.plan) cudaFree(s.plan);
+    if (s.fscratch) cudaFree(s.fscratch);
+    if (s.render_owner) cudaFree(s.render_owner);
+    if (s.render_img) cudaFree(s.render_img);
     if (s.p2p_err) cudaFree(s.p2p_err);
+    for (cudaEvent_t e : s.prof_ev)
+        if (e) cudaEventDestroy(e);
     if (s.ev0) cudaEventDestroy(s.ev0);
     if (s.ev1) cudaEventDestroy(s.ev1);
+    if (s.ev_copy) cudaEventDestroy(s.ev_copy);
     if (s.comm) {
         const NcclApi *api = nccl_api(nullptr);
         if (api) api->CommDestroy(s.comm);
@@ -204,18 +265,37 @@ static void free_shard(Shard &s)
     s = Shard();
 }
 
-static ForceArgs force_args(const nbody_gpu *h, const Shard &s, int slot)
+// A failed CUDA / NCCL call inside a step, an upload or a fetch leaves the device state undefined: the handle
+// remembers the first such failure and every later call returns it instead of computing on garbage.
+static int poison(nbody_gpu *h, int rc)
+{
+    if (rc != NBODY_GPU_OK && rc != NBODY_GPU_EINVAL && !h->failed_rc) {
+        h->failed_rc = rc;
+        snprintf(h->failed_msg, sizeof h->failed_msg, "%s", g_err);
+    }
+    return rc;
+}
+
+static int check_usable(const nbody_gpu *h)
+{
+    if (!h) return fail(NBODY_GPU_EINVAL, "handle is NULL");
+    if (h->failed_rc) return fail(h->failed_rc, "handle is unusable after an earlier failure: %.400s", h->failed_msg);
+    return NBODY_GPU_OK;
+}
+
+// Does the velocity / force state live sharded between steps (own rows only on each device)?
+static bool state_sharded(const nbody_gpu *h) { return h->sharded && (!h->symmetric || h->p2p); }
+
+static ForceArgs force_args(const nbody_gpu *h, const Shard &s, int slot, double2 *exact_out)
 {
     ForceArgs a;
     a.pos = s.pos[slot];
     a.mr = s.mr;
-    a.out = (h->cfg.mode == NBODY_GPU_MODE_FAST) ? s.part : s.frc;
+    a.out = (h->cfg.mode == NBODY_GPU_MODE_FAST) ? s.part : exact_out;
     a.n = h->n;
     a.npad = h->npad;
-    // symmetric kernel: every device holds the complete force vectors after the exchange and integrates
-    // ALL bodies (identical bits everywhere), which saves the position all-gather
-    a.lo = h->symmetric ? 0 : s.lo;
-    a.hi = h->symmetric ? h->n : s.hi;
+    a.lo = s.lo;
+    a.hi = s.hi;
     a.chunk = h->chunk;
     return a;
 }
@@ -232,29 +312,36 @@ static IntegrateArgs integrate_args(const nbody_gpu *h, const Shard &s, int slot
     a.vbuf = h->symmetric ? s.vbuf : nullptr;
     a.nsplit = h->nsplit;
     a.npad = h->npad;
-    // symmetric kernel: every device holds the complete force vectors after the exchange and integrates
-    // ALL bodies (identical bits everywhere), which saves the position all-gather
-    // (with the fused peer exchange each device integrates its own rows and stores the new positions to all)
+    a.n = h->n;
+    // symmetric kernel with the NCCL exchange: every device holds the complete force vectors after the
+    // all-gather and integrates ALL bodies (identical bits everywhere), which saves the position all-gather;
+    // with the fused peer exchange each device integrates its own rows and stores the new positions to all
     const bool all_rows = h->symmetric && !h->p2p;
     a.lo = all_rows ? 0 : s.lo;
     a.hi = all_rows ? h->n : s.hi;
     a.xdim = h->cfg.xdim;
     a.ydim = h->cfg.ydim;
     a.npeers = 0;
-    for (int r = 0; r < MAX_PEERS; ++r) a.peer_pos_new[r] = nullptr;
+    a.boxes = h->fused_boxes ? s.boxes : nullptr;
+    for (int r = 0; r < MAX_PEERS; ++r) {
+        a.peer_pos_new[r] = nullptr;
+        a.peer_boxes[r] = nullptr;
+    }
     if (h->p2p) {
         a.npeers = s.peers.npeers;
-        for (int r = 0; r < s.peers.npeers; ++r) a.peer_pos_new[r] = s.peers.pos[slot ^ 1][r];
+        for (int r = 0; r < s.peers.npeers; ++r) {
+            a.peer_pos_new[r] = s.peers.pos[slot ^ 1][r];
+            a.peer_boxes[r] = s.peers.boxes[r];
+        }
     }
     return a;
 }
 
-// Enqueue the force kernel of shard s on the positions in slot `slot` (for the symmetric kernel also
-// the fold of its partial sums into this device's virtual-rank vectors).
-static void enqueue_forces(nbody_gpu *h, Shard &s, int slot)
+// Enqueue the force kernel of shard s on the positions in slot `slot`.
+static int enqueue_forces(nbody_gpu *h, Shard &s, int slot, double2 *exact_out)
 {
     if (h->cfg.mode != NBODY_GPU_MODE_FAST) {
-        launch_forces_exact(force_args(h, s, slot), s.stream);
+        NB_LAUNCH_RC(launch_forces_exact(force_args(h, s, slot, exact_out), s.stream));
     } else if (h->symmetric) {
         SymArgs a;
         a.pos = s.pos[slot];
@@ -262,20 +349,24 @@ static void enqueue_forces(nbody_gpu *h, Shard &s, int slot)
         a.rowpart = s.part;
         a.colpart = s.colpart;
         a.boxes = s.boxes;
-        a.counter = s.sym_counter;
         a.n = h->n;
         a.npad = h->npad;
-        a.chunk = h->chunk;
+        a.cm = h->cm;
         a.v0 = s.v0;
         a.nv = s.nv;
-        if (s.boxes) launch_tile_boxes(s.pos[slot], s.mr, h->n, s.boxes, s.stream);
-        launch_forces_sym(a, s.nblocks_owned, h->nsplit, s.stream);
+        if (h->sorted && !h->fused_boxes) {   // shard boundaries cut through tiles: the boxes get their own launch
+            launch_tile_boxes(s.pos[slot], s.mr, h->n, s.boxes, s.stream);
+            h->launches[2] += 1;
+        }
+        NB_LAUNCH_RC(launch_forces_sym(a, s.nblocks_owned, s.stream));
     } else {
-        launch_forces_fast(force_args(h, s, slot), h->nsplit, s.stream);
+        launch_forces_fast(force_args(h, s, slot, nullptr), h->nsplit, s.stream);
     }
+    h->launches[0] += 1;
+    return NBODY_GPU_OK;
 }
 
-static void enqueue_sym_reduce(nbody_gpu *h, Shard &s, bool to_peers = false)
+static void enqueue_sym_reduce(nbody_gpu *h, Shard &s, bool to_peers)
 {
     SymReduceArgs a;
     a.rowpart = s.part;
@@ -283,25 +374,28 @@ static void enqueue_sym_reduce(nbody_gpu *h, Shard &s, bool to_peers = false)
     a.vbuf = s.vbuf;
     a.n = h->n;
     a.npad = h->npad;
-    a.chunk = h->chunk;
-    a.nsplit = h->nsplit;
+    a.cm = h->cm;
     a.v0 = s.v0;
     a.nv = s.nv;
     if (to_peers) launch_sym_reduce_p2p(a, s.peers, h->rows_per_shard, s.stream);
     else launch_sym_reduce(a, s.stream);
+    h->launches[2] += 1;
 }
 
 static void enqueue_integrate(nbody_gpu *h, Shard &s, int slot)
 {
     if (h->cfg.mode == NBODY_GPU_MODE_FAST) launch_integrate_fast(integrate_args(h, s, slot), s.stream);
     else launch_integrate_exact(integrate_args(h, s, slot), s.stream);
+    h->launches[1] += 1;
 }
 
-}  // namespace nbody
+static void enqueue_barrier(nbody_gpu *h, Shard &s, int phase)
+{
+    launch_p2p_barrier(s.peers, phase, s.p2p_err, s.stream);
+    h->launches[2] += 1;
+}
 
-namespace nbody {
-
-enum { AG_POS0 = 0, AG_POS1 = 1, AG_VEL = 2, AG_FRC = 3, AG_VBUF = 4 };
+enum { AG_POS0 = 0, AG_POS1 = 1, AG_VEL = 2, AG_FRC = 3, AG_VBUF = 4, AG_SCRATCH = 5 };
 
 // In-place all-gather on every local shard.  Row arrays (npad double2, shard r's rows at
 // [r*rows_per_shard, ...)) replace MPI_Allgatherv (reference nbody-par.c:913-917); AG_VBUF gathers the
@@ -321,7 +415,8 @@ static int allgather(nbody_gpu *h, int which)
             buf = s.vbuf;
             per_shard = static_cast<size_t>(s.nv) * h->npad;
         } else {
-            buf = which == AG_POS0 ? s.pos[0] : which == AG_POS1 ? s.pos[1] : which == AG_VEL ? s.vel : s.frc;
+            buf = which == AG_POS0 ? s.pos[0] : which == AG_POS1 ? s.pos[1] : which == AG_VEL ? s.vel
+                : which == AG_FRC ? s.frc : s.fscratch;
             per_shard = static_cast<size_t>(h->rows_per_shard);
         }
         const double2 *send = buf + static_cast<size_t>(s.part_index) * per_shard;
@@ -332,15 +427,50 @@ static int allgather(nbody_gpu *h, int which)
     return NBODY_GPU_OK;
 }
 
+// Make the sharded velocity / force arrays complete on every device (before a fetch or a re-sort; what the
+// reference's whole-struct MPI_Allgatherv does every step, nbody-par.c:933-936).  Peer-mapped jobs: every device
+// stores its rows into all peers between two barriers; otherwise two ncclAllGather calls.
+static int complete_state(nbody_gpu *h, bool want_vel, bool want_frc)
+{
+    if (!state_sharded(h) || (!want_vel && !want_frc)) return NBODY_GPU_OK;
+    if (!h->p2p) {
+        int rc = want_vel ? allgather(h, AG_VEL) : NBODY_GPU_OK;
+        if (!rc && want_frc) rc = allgather(h, AG_FRC);
+        return rc;
+    }
+    for (Shard &s : h->shards) {   // nobody is still working on the arrays we are about to store into
+        NB_CUDA(cudaSetDevice(s.device));
+        enqueue_barrier(h, s, 2);
+    }
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        PublishArgs p;
+        p.src[0] = want_vel ? s.vel : nullptr;
+        p.src[1] = want_frc ? s.frc : nullptr;
+        for (int r = 0; r < MAX_PEERS; ++r) {
+            p.dst[0][r] = r < s.peers.npeers ? s.peers.vel[r] : nullptr;
+            p.dst[1][r] = r < s.peers.npeers ? s.peers.frc[r] : nullptr;
+        }
+        p.npeers = s.peers.npeers;
+        p.me = s.peers.me;
+        p.lo = s.lo;
+        p.hi = s.hi;
+        launch_publish(p, s.stream);
+        h->launches[2] += 1;
+        enqueue_barrier(h, s, 2);
+        NB_CUDA(cudaGetLastError());
+    }
+    return NBODY_GPU_OK;
+}
+
 // Put every local shard's arrays into cell order (kernels_sort.cu).  All devices hold the same positions, so
-// they all arrive at the same permutation without talking to each other; with the fused peer exchange the
-// velocities and last forces live sharded and are gathered first (`gather`).
+// they all arrive at the same permutation without talking to each other; sharded velocities and last forces
+// are completed first (`gather`).  Ends with the tile boxes of the new order.
 static int resort(nbody_gpu *h, bool gather)
 {
     if (!h->sorted) return NBODY_GPU_OK;
-    if (gather && h->sharded && h->p2p) {
-        int rc = allgather(h, AG_VEL);
-        if (!rc) rc = allgather(h, AG_FRC);
+    if (gather) {
+        int rc = complete_state(h, true, true);
         if (rc) return rc;
     }
     const double scale = 65535.0 / static_cast<double>(h->cfg.xdim > h->cfg.ydim ? h->cfg.xdim : h->cfg.ydim);
@@ -371,9 +501,10 @@ static int resort(nbody_gpu *h, bool gather)
         NB_CUDA(cudaMemcpyAsync(s.vel, s.gat[2], bytes, cudaMemcpyDeviceToDevice, s.stream));
         NB_CUDA(cudaMemcpyAsync(s.frc, s.gat[3], bytes, cudaMemcpyDeviceToDevice, s.stream));
         NB_CUDA(cudaMemcpyAsync(s.orig, s.orig_tmp, sizeof(int) * static_cast<size_t>(h->n), cudaMemcpyDeviceToDevice, s.stream));
+        launch_tile_boxes(s.pos[h->cur], s.mr, h->n, s.boxes, s.stream);
         NB_CUDA(cudaGetLastError());
     }
-    h->launches[2] += static_cast<long long>(h->shards.size()) * 3;
+    h->launches[2] += static_cast<long long>(h->shards.size()) * 4;
     h->since_sort = 0;
     h->sorts += 1;
     return NBODY_GPU_OK;
@@ -387,7 +518,7 @@ static int maybe_resort(nbody_gpu *h)
     return NBODY_GPU_OK;
 }
 
-// Optional per-phase event hooks for nbody_gpu_step_profiled: mark(shard index, phase 0..4).
+// Optional per-phase event hooks for nbody_gpu_step_profiled: mark(shard index, phase 0..5).
 struct StepMarks {
     virtual int mark(size_t shard, int phase) = 0;
     virtual ~StepMarks() {}
@@ -396,7 +527,7 @@ struct StepMarks {
 // One step on every local shard, reading slot h->cur:
 //   forces [+ symmetric fold] | exchange A (symmetric & sharded: the virtual-rank force vectors)
 //   | integrate | exchange B (the new positions) | flip.
-// Exchanges: fused peer-memory stores + signal/wait kernels (h->p2p), else ncclAllGather.
+// Exchanges: fused peer-memory stores + barrier kernels (h->p2p), else ncclAllGather.
 // Phases for marks: 0 start, 1 after forces, 2 after fold, 3 after exchange A, 4 after integrate, 5 after exchange B.
 static int run_one_step(nbody_gpu *h, StepMarks *marks)
 {
@@ -413,29 +544,24 @@ static int run_one_step(nbody_gpu *h, StepMarks *marks)
         if (rc) return rc;
     }
     NB_MARK(0)
-    h->epoch += 1;
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
-        enqueue_forces(h, s, h->cur);
+        int rc = enqueue_forces(h, s, h->cur, s.frc);
+        if (rc) return rc;
     }
-    h->launches[0] += static_cast<long long>(nsh);
-    if (h->sorted) h->launches[2] += static_cast<long long>(nsh);   // tile_boxes_kernel
     NB_MARK(1)
     if (h->symmetric) {
         for (Shard &s : h->shards) {
             NB_CUDA(cudaSetDevice(s.device));
             enqueue_sym_reduce(h, s, h->p2p);
-            if (h->p2p) launch_p2p_signal(s.peers, 0, h->epoch, s.stream);
         }
-        h->launches[2] += static_cast<long long>(nsh) * (h->p2p ? 2 : 1);
     }
     NB_MARK(2)
     if (h->p2p) {
         for (Shard &s : h->shards) {
             NB_CUDA(cudaSetDevice(s.device));
-            launch_p2p_wait(s.peers, 0, h->epoch, s.p2p_err, s.stream);
+            enqueue_barrier(h, s, 0);
         }
-        h->launches[2] += static_cast<long long>(nsh);
     } else if (h->symmetric) {
         int rc = allgather(h, AG_VBUF);
         if (rc) return rc;
@@ -444,16 +570,13 @@ static int run_one_step(nbody_gpu *h, StepMarks *marks)
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
         enqueue_integrate(h, s, h->cur);
-        if (h->p2p) launch_p2p_signal(s.peers, 1, h->epoch, s.stream);
     }
-    h->launches[1] += static_cast<long long>(nsh);
     NB_MARK(4)
     if (h->p2p) {
         for (Shard &s : h->shards) {
             NB_CUDA(cudaSetDevice(s.device));
-            launch_p2p_wait(s.peers, 1, h->epoch, s.p2p_err, s.stream);
+            enqueue_barrier(h, s, 1);
         }
-        h->launches[2] += static_cast<long long>(nsh) * 2;
     } else if (!h->symmetric) {
         int rc = allgather(h, h->cur ^ 1);
         if (rc) return rc;
@@ -465,33 +588,32 @@ static int run_one_step(nbody_gpu *h, StepMarks *marks)
     return NBODY_GPU_OK;
 }
 
-// Interleave two host arrays into pinned staging buffer `buf` and enqueue one H2D copy per local device.
-// The caller synchronises (sync_all) before the staging buffer is used again.
-static int upload(nbody_gpu *h, double2 *Shard::*field, int slot, const double *a, const double *b, int buf)
-{
-    double2 *stage = h->stage + static_cast<size_t>(buf) * h->npad;
-    for (int i = 0; i < h->n; ++i) stage[i] = make_double2(a ? a[i] : 0.0, b ? b[i] : 0.0);
-    for (int i = h->n; i < h->npad; ++i) stage[i] = make_double2(0.0, 0.0);
-    for (Shard &s : h->shards) {
-        NB_CUDA(cudaSetDevice(s.device));
-        double2 *dst = field ? s.*field : s.pos[slot];
-        NB_CUDA(cudaMemcpyAsync(dst, stage, sizeof(double2) * h->npad, cudaMemcpyHostToDevice, s.stream));
-    }
-    return NBODY_GPU_OK;
-}
-
+// The step loop as a CUDA graph: h->graph_steps steps (even: the slot parity is preserved) of shard s, starting
+// from slot `start_slot`.  One device, or a shard of a peer-mapped job (the barrier kernels keep their own
+// counts in device memory, so nothing in the graph changes from launch to launch).
 static int build_graph(nbody_gpu *h, Shard &s, int start_slot)
 {
     cudaGraph_t g = nullptr;
+    long long keep[4];
+    memcpy(keep, h->launches, sizeof keep);   // counted at launch time, not at capture time
     NB_CUDA(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
     int slot = start_slot;
-    for (int k = 0; k < h->graph_steps; ++k) {
-        enqueue_forces(h, s, slot);
-        if (h->symmetric) enqueue_sym_reduce(h, s);
+    int rc = NBODY_GPU_OK;
+    for (int k = 0; k < h->graph_steps && !rc; ++k) {
+        rc = enqueue_forces(h, s, slot, s.frc);
+        if (rc) break;
+        if (h->symmetric) enqueue_sym_reduce(h, s, h->p2p);
+        if (h->p2p) enqueue_barrier(h, s, 0);
         enqueue_integrate(h, s, slot);
+        if (h->p2p) enqueue_barrier(h, s, 1);
         slot ^= 1;
     }
     cudaError_t e = cudaStreamEndCapture(s.stream, &g);
+    memcpy(h->launches, keep, sizeof keep);
+    if (rc) {
+        if (g) cudaGraphDestroy(g);
+        return rc;
+    }
     if (e != cudaSuccess) return fail(NBODY_GPU_ECUDA, "graph capture failed: %s", cudaGetErrorString(e));
     e = cudaGraphInstantiate(&s.graph[start_slot], g, 0);
     cudaGraphDestroy(g);
@@ -507,36 +629,70 @@ static int sync_all(nbody_gpu *h)
         if (h->p2p && s.p2p_err) {
             int e = 0;
             NB_CUDA(cudaMemcpy(&e, s.p2p_err, sizeof e, cudaMemcpyDeviceToHost));
-            if (e) return fail(NBODY_GPU_ECUDA, "peer exchange %c timed out waiting for another GPU", e == 1 ? 'A' : 'B');
+            if (e) return fail(NBODY_GPU_ECUDA, "peer exchange %c timed out waiting for another GPU", e == 1 ? 'A' : e == 2 ? 'B' : 'S');
         }
     }
     return NBODY_GPU_OK;
+}
+
+// Kernel launches of one step of one shard (for the launch counters of a graph launch).
+static void count_graph_launch(nbody_gpu *h)
+{
+    const long long k = h->graph_steps;
+    h->launches[0] += k;
+    h->launches[1] += k;
+    long long other = 0;
+    if (h->symmetric) other += 1;                          // fold
+    if (h->sorted && !h->fused_boxes) other += 1;          // tile boxes
+    if (h->p2p) other += 2;                                // barriers
+    h->launches[2] += k * other;
 }
 
 static int do_steps(nbody_gpu *h, int steps)
 {
     if (steps < 0) return fail(NBODY_GPU_EINVAL, "steps must be >= 0");
     int left = steps;
-    if (!h->sharded && h->graph_steps > 0) {
+    if (h->small && left > 0) {
+        // the whole loop in one launch: the world lives in shared memory (smalln.cuh)
         Shard &s = h->shards[0];
         NB_CUDA(cudaSetDevice(s.device));
+        SmallArgs a;
+        a.pos[0] = s.pos[0];
+        a.pos[1] = s.pos[1];
+        a.mr = s.mr;
+        a.vel = s.vel;
+        a.frc = s.frc;
+        a.n = h->n;
+        a.steps = left;
+        a.cur = h->cur;
+        a.xdim = h->cfg.xdim;
+        a.ydim = h->cfg.ydim;
+        NB_LAUNCH_RC(launch_small_world(a, s.stream));
+        h->launches[0] += 1;
+        h->cur ^= (left & 1);
+        left = 0;
+    }
+    if (h->graph_steps > 0 && (!h->sharded || h->p2p)) {
         while (left >= h->graph_steps) {
             if (h->sorted && h->since_sort + h->graph_steps > h->sort_interval) {
                 // a re-sort is due before or inside the next graph launch: single steps until it has happened
                 int rc = run_one_step(h, nullptr);
                 if (rc) return rc;
                 left -= 1;
-                NB_CUDA(cudaSetDevice(s.device));
                 continue;
             }
-            if (!s.graph[h->cur]) {
-                int rc = build_graph(h, s, h->cur);
-                if (rc) return rc;
+            for (Shard &s : h->shards) {
+                NB_CUDA(cudaSetDevice(s.device));
+                if (!s.graph[h->cur]) {
+                    int rc = build_graph(h, s, h->cur);
+                    if (rc) return rc;
+                }
             }
-            NB_CUDA(cudaGraphLaunch(s.graph[h->cur], s.stream));
-            h->launches[0] += h->graph_steps;
-            h->launches[1] += h->graph_steps;
-            if (h->symmetric) h->launches[2] += h->graph_steps * (h->sorted ? 2 : 1);
+            for (Shard &s : h->shards) {
+                NB_CUDA(cudaSetDevice(s.device));
+                NB_CUDA(cudaGraphLaunch(s.graph[h->cur], s.stream));
+                count_graph_launch(h);
+            }
             h->since_sort += h->graph_steps;
             left -= h->graph_steps;   // graph_steps is even: h->cur is unchanged
         }
@@ -552,21 +708,37 @@ static int do_steps(nbody_gpu *h, int steps)
     return NBODY_GPU_OK;
 }
 
+static void point_into_arena(const ArenaLayout &L, unsigned char *base, double2 **pos0, double2 **pos1, double2 **vel,
+                             double2 **frc, double2 **vbuf, double **boxes, unsigned long long **flags)
+{
+    *pos0 = reinterpret_cast<double2 *>(base + L.pos[0]);
+    *pos1 = reinterpret_cast<double2 *>(base + L.pos[1]);
+    *vel = reinterpret_cast<double2 *>(base + L.vel);
+    *frc = reinterpret_cast<double2 *>(base + L.frc);
+    *vbuf = reinterpret_cast<double2 *>(base + L.vbuf);
+    *boxes = reinterpret_cast<double *>(base + L.boxes);
+    *flags = reinterpret_cast<unsigned long long *>(base + L.flags);
+}
+
+static void fill_peer(Shard &s, const ArenaLayout &L, int r, unsigned char *base)
+{
+    point_into_arena(L, base, &s.peers.pos[0][r], &s.peers.pos[1][r], &s.peers.vel[r], &s.peers.frc[r], &s.peers.vbuf[r],
+                     &s.peers.boxes[r], &s.peers.flags[r]);
+}
 
 // Build the peer-memory tables for the fused exchange.  Single process: cudaDeviceEnablePeerAccess between
-// all local devices.  One process per GPU: CUDA IPC handles of vbuf / pos[0] / pos[1] / flags, all-gathered
-// through the NCCL communicator that already exists for the bootstrap.  Returns NBODY_GPU_OK with
-// h->p2p = false when peer access is not possible (the NCCL path is then used).
+// all local devices.  One process per GPU: one CUDA IPC handle per rank (the arena), all-gathered through the
+// NCCL communicator that already exists for the bootstrap.  Returns NBODY_GPU_OK with h->p2p = false when peer
+// access is not possible (the NCCL path is then used).
 static int setup_p2p(nbody_gpu *h)
 {
     const int P = h->nshards_total;
     if (P > MAX_PEERS) return NBODY_GPU_OK;
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
-        NB_CUDA(cudaMalloc(&s.flags, sizeof(unsigned long long) * 2 * MAX_PEERS));
-        NB_CUDA(cudaMemset(s.flags, 0, sizeof(unsigned long long) * 2 * MAX_PEERS));
         NB_CUDA(cudaMalloc(&s.p2p_err, sizeof(int)));
-        NB_CUDA(cudaMemset(s.p2p_err, 0, sizeof(int)));
+        NB_CUDA(cudaMemsetAsync(s.p2p_err, 0, sizeof(int), s.stream));
+        s.peers.epoch = s.epoch;
     }
     if (h->shards.size() > 1) {   // one process, several devices
         for (Shard &a : h->shards) {
@@ -584,12 +756,12 @@ static int setup_p2p(nbody_gpu *h)
         for (Shard &a : h->shards) {
             a.peers.npeers = P;
             a.peers.me = a.part_index;
-            for (Shard &b : h->shards) {
-                a.peers.vbuf[b.part_index] = b.vbuf;
-                a.peers.pos[0][b.part_index] = b.pos[0];
-                a.peers.pos[1][b.part_index] = b.pos[1];
-                a.peers.flags[b.part_index] = b.flags;
-            }
+            for (Shard &b : h->shards) fill_peer(a, h->lay, b.part_index, b.arena);
+        }
+        // the arenas are zeroed (flags, counts) before any device signals into them
+        for (Shard &s : h->shards) {
+            NB_CUDA(cudaSetDevice(s.device));
+            NB_CUDA(cudaStreamSynchronize(s.stream));
         }
         h->p2p = true;
         return NBODY_GPU_OK;
@@ -598,27 +770,20 @@ static int setup_p2p(nbody_gpu *h)
     Shard &s = h->shards[0];
     const NcclApi *api = nccl_api(nullptr);
     if (!api) return NBODY_GPU_OK;
-    struct Handles { cudaIpcMemHandle_t m[4]; };
-    static_assert(sizeof(Handles) % sizeof(double) == 0, "handles travel as doubles");
-    Handles mine;
-    void *ptrs[4] = {s.vbuf, s.pos[0], s.pos[1], s.flags};
+    struct Packet { cudaIpcMemHandle_t m; double ok; };
+    static_assert(sizeof(Packet) % sizeof(double) == 0, "packets travel as doubles");
+    Packet pk;
     NB_CUDA(cudaSetDevice(s.device));
-    int ipc_ok = 1;
-    for (int k = 0; k < 4; ++k) {
-        if (cudaIpcGetMemHandle(&mine.m[k], ptrs[k]) != cudaSuccess) {
-            cudaGetLastError();
-            ipc_ok = 0;
-            memset(&mine.m[k], 0, sizeof mine.m[k]);
-        }
+    pk.ok = 1.0;
+    if (cudaIpcGetMemHandle(&pk.m, s.arena) != cudaSuccess) {
+        cudaGetLastError();
+        pk.ok = 0.0;
+        memset(&pk.m, 0, sizeof pk.m);
     }
     // every rank must take the same decision: gather the handles plus an "ok" marker
-    struct Packet { Handles h; double ok; };
     Packet *dev = nullptr;
     std::vector<Packet> all(P);
     NB_CUDA(cudaMalloc(&dev, sizeof(Packet) * P));
-    Packet pk;
-    pk.h = mine;
-    pk.ok = ipc_ok;
     NB_CUDA(cudaMemcpyAsync(dev + s.part_index, &pk, sizeof pk, cudaMemcpyHostToDevice, s.stream));
     NB_NCCL(api, api->AllGather(dev + s.part_index, dev, sizeof(Packet) / sizeof(double), NCCL_DOUBLE, s.comm, s.stream));
     NB_CUDA(cudaMemcpyAsync(all.data(), dev, sizeof(Packet) * P, cudaMemcpyDeviceToHost, s.stream));
@@ -630,24 +795,18 @@ static int setup_p2p(nbody_gpu *h)
     s.peers.me = s.part_index;
     int opened_all = 1;
     for (int r = 0; r < P; ++r) {
-        void *q[4];
-        if (r == s.part_index) {
-            for (int k = 0; k < 4; ++k) q[k] = ptrs[k];
-        } else {
-            for (int k = 0; k < 4; ++k) {
-                q[k] = nullptr;
-                if (cudaIpcOpenMemHandle(&q[k], all[r].h.m[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
-                    cudaGetLastError();
-                    opened_all = 0;
-                } else {
-                    s.ipc_opened.push_back(q[k]);
-                }
+        void *q = s.arena;
+        if (r != s.part_index) {
+            q = nullptr;
+            if (cudaIpcOpenMemHandle(&q, all[r].m, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                cudaGetLastError();
+                opened_all = 0;
+                q = s.arena;   // never dereferenced: the ranks agree below not to use the table
+            } else {
+                s.ipc_opened.push_back(q);
             }
         }
-        s.peers.vbuf[r] = static_cast<double2 *>(q[0]);
-        s.peers.pos[0][r] = static_cast<double2 *>(q[1]);
-        s.peers.pos[1][r] = static_cast<double2 *>(q[2]);
-        s.peers.flags[r] = static_cast<unsigned long long *>(q[3]);
+        fill_peer(s, h->lay, r, static_cast<unsigned char *>(q));
     }
     // agree on the outcome (a rank that could not map a peer must not leave the others waiting for it)
     double *flag = nullptr;
@@ -662,6 +821,72 @@ static int setup_p2p(nbody_gpu *h)
     for (int r = 0; r < P; ++r)
         if (oks[r] != 1.0) return NBODY_GPU_OK;
     h->p2p = true;
+    return NBODY_GPU_OK;
+}
+
+// Upload the caller's planar arrays (body order) into slot `slot` and the velocity array; mass/radius too when
+// given (init).  One H2D copy per array straight from the caller's memory -- at full PCIe speed when the caller
+// registered it (nbody_gpu_pin_host), staged by the driver when it is pageable -- then a kernel interleaves into
+// the double2 arrays.  Peer-mapped jobs: every rank uploads only ITS rows and the kernel stores them into every
+// device (between two barriers), like the root's MPI_Bcast but with each rank sending an eighth
+// (nbody-par.c:874).  Returns after the copies have left the host buffers; the kernels may still be queued.
+static int upload_state(nbody_gpu *h, int slot, const double *x, const double *y, const double *xv, const double *yv,
+                        const double *mass, const double *radius)
+{
+    const size_t np = static_cast<size_t>(h->npad);
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        const int ulo = h->p2p ? s.lo : 0, uhi = h->p2p ? s.hi : h->n;
+        const size_t cnt = static_cast<size_t>(uhi > ulo ? uhi - ulo : 0) * sizeof(double);
+        const double *src[4] = {x, y, xv, yv};
+        for (int k = 0; k < 4; ++k)
+            if (cnt) NB_CUDA(cudaMemcpyAsync(s.plan + k * np + ulo, src[k] + ulo, cnt, cudaMemcpyHostToDevice, s.stream));
+        if (mass && radius) {
+            NB_CUDA(cudaMemcpyAsync(s.plan + 4 * np, mass, sizeof(double) * h->n, cudaMemcpyHostToDevice, s.stream));
+            NB_CUDA(cudaMemcpyAsync(s.plan + 5 * np, radius, sizeof(double) * h->n, cudaMemcpyHostToDevice, s.stream));
+        }
+        NB_CUDA(cudaEventRecord(s.ev_copy, s.stream));
+    }
+    if (h->p2p) {
+        for (Shard &s : h->shards) {   // no peer is still reading the arrays we are about to store into
+            NB_CUDA(cudaSetDevice(s.device));
+            enqueue_barrier(h, s, 2);
+        }
+    }
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        ScatterArgs a;
+        a.lo = h->p2p ? s.lo : 0;
+        a.hi = h->p2p ? s.hi : h->n;
+        for (int r = 0; r < MAX_PEERS; ++r) a.dst[r] = nullptr;
+        a.a = s.plan;
+        a.b = s.plan + np;
+        a.ndst = h->p2p ? s.peers.npeers : 1;
+        for (int r = 0; r < a.ndst; ++r) a.dst[r] = h->p2p ? s.peers.pos[slot][r] : s.pos[slot];
+        launch_scatter(a, s.stream);
+        a.a = s.plan + 2 * np;
+        a.b = s.plan + 3 * np;
+        for (int r = 0; r < a.ndst; ++r) a.dst[r] = h->p2p ? s.peers.vel[r] : s.vel;
+        launch_scatter(a, s.stream);
+        h->launches[2] += 2;
+        if (mass && radius) {
+            a.lo = 0;
+            a.hi = h->n;
+            a.a = s.plan + 4 * np;
+            a.b = s.plan + 5 * np;
+            a.ndst = 1;
+            a.dst[0] = s.mr;
+            launch_scatter(a, s.stream);
+            h->launches[2] += 1;
+        }
+        NB_CUDA(cudaMemsetAsync(s.frc, 0, sizeof(double2) * np, s.stream));
+        if (h->p2p) enqueue_barrier(h, s, 2);
+        NB_CUDA(cudaGetLastError());
+    }
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        NB_CUDA(cudaEventSynchronize(s.ev_copy));
+    }
     return NBODY_GPU_OK;
 }
 
@@ -735,11 +960,43 @@ int nbody_gpu_nccl_unique_id(void *out)
     return NBODY_GPU_OK;
 }
 
+int nbody_gpu_pin_host(void *ptr, size_t bytes)
+{
+    if (!ptr || !bytes) return fail(NBODY_GPU_EINVAL, "NULL or empty range");
+    cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterPortable);
+    if (e == cudaErrorHostMemoryAlreadyRegistered) {
+        cudaGetLastError();
+        return NBODY_GPU_OK;
+    }
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(NBODY_GPU_ECUDA, "cudaHostRegister(%p, %zu) failed: %s", ptr, bytes, cudaGetErrorString(e));
+    }
+    return NBODY_GPU_OK;
+}
+
+int nbody_gpu_unpin_host(void *ptr)
+{
+    if (!ptr) return fail(NBODY_GPU_EINVAL, "NULL pointer");
+    cudaError_t e = cudaHostUnregister(ptr);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(NBODY_GPU_ECUDA, "cudaHostUnregister(%p) failed: %s", ptr, cudaGetErrorString(e));
+    }
+    return NBODY_GPU_OK;
+}
+
 void nbody_gpu_destroy(nbody_gpu *h)
 {
     if (!h) return;
+    for (Shard &s : h->shards) {   // nothing of ours is still running when the memory goes away
+        if (s.stream) {
+            cudaSetDevice(s.device);
+            cudaStreamSynchronize(s.stream);
+        }
+    }
     for (Shard &s : h->shards) free_shard(s);
-    if (h->stage) cudaFreeHost(h->stage);
+    cudaGetLastError();
     delete h;
 }
 
@@ -759,25 +1016,44 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
         return fail(NBODY_GPU_EINVAL, "ngpus = %d but only %d CUDA devices are visible", cfg->ngpus, ndev);
     if (multi_rank && (cfg->rank < 0 || cfg->rank >= cfg->nranks || !cfg->nccl_id))
         return fail(NBODY_GPU_EINVAL, "multi-rank init needs 0 <= rank < nranks and nccl_id");
+    if (cfg->sort_interval < 0) return fail(NBODY_GPU_EINVAL, "sort_interval must be >= 0");
     h->nshards_total = P;
     h->sharded = P > 1;
     h->rows_per_shard = (h->n + P - 1) / P;
     h->npad = h->rows_per_shard * P;
-    h->symmetric = cfg->mode == NBODY_GPU_MODE_FAST && (SYM_V % P == 0) &&
-                   (cfg->symmetric > 0 || (cfg->symmetric == 0 && h->n >= 8192));
+    const bool fast = cfg->mode == NBODY_GPU_MODE_FAST;
+    h->symmetric = fast && (SYM_V % P == 0) && (cfg->symmetric > 0 || (cfg->symmetric == 0 && h->n >= 8192));
     h->nblocks = (h->n + SYM_RB - 1) / SYM_RB;
-    h->sorted = h->symmetric && (cfg->sort > 0 || (cfg->sort == 0 && h->n >= 16384));
-    h->sort_interval = 256;
-    if (const char *e = getenv("NBODY_SORT_INTERVAL")) {   // development knob
-        if (atoi(e) > 0) h->sort_interval = atoi(e);
+    const size_t bytes = sizeof(double2) * static_cast<size_t>(h->npad);
+    if (h->symmetric) {
+        h->cm = choose_split_sym(h->n, cfg->jsplit);
+        // the reaction partial sums grow with n^2: when they do not fit the device, the directed
+        // kernel (2x the pair evaluations, O(n) memory) runs instead
+        const size_t slots = static_cast<size_t>((h->nblocks + 2 * SYM_V - 1) / (2 * SYM_V)) * 2 * (SYM_V / P);
+        size_t free_b = 0, total_b = 0;
+        if (multi_dev) NB_CUDA(cudaSetDevice(0));
+        else if (cfg->device >= 0) NB_CUDA(cudaSetDevice(cfg->device));
+        NB_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        const double need = static_cast<double>(bytes) * (static_cast<double>(slots) + h->cm.nsplit + 24.0);
+        if (need > 0.92 * static_cast<double>(free_b)) {
+            if (cfg->symmetric > 0)
+                return fail(NBODY_GPU_ENOMEM, "the symmetric kernel needs %.1f GB of partial sums for n = %d on %d GPU(s), %.1f GB are free",
+                            need / 1e9, h->n, P, free_b / 1e9);
+            h->symmetric = false;
+        }
     }
-    if (h->symmetric) choose_split_sym(h->n, cfg->jsplit, &h->nsplit, &h->chunk);
-    else if (cfg->mode == NBODY_GPU_MODE_FAST) choose_split(h->n, cfg->jsplit, &h->nsplit, &h->chunk);
+    h->sorted = h->symmetric && (cfg->sort > 0 || (cfg->sort == 0 && h->n >= 16384));
+    h->sort_interval = cfg->sort_interval > 0 ? cfg->sort_interval : 256;
+    h->fused_boxes = h->sorted && (P == 1 || h->rows_per_shard % TILE_J == 0);
+    if (h->symmetric) h->nsplit = h->cm.nsplit;
+    else if (fast) choose_split(h->n, cfg->jsplit, &h->nsplit, &h->chunk);
     else { h->nsplit = 1; h->chunk = h->n; }
-    if (cfg->use_graph >= 0 && !h->sharded) {
+    h->small = !fast && !h->sharded && h->n <= SMALL_N_MAX && cfg->use_graph >= 0;
+    if (cfg->use_graph >= 0) {
         // small worlds are launch-bound: put more steps behind one graph launch
         h->graph_steps = (h->n <= 2048) ? 32 : (h->n <= 16384 ? 8 : 2);
     }
+    h->lay = arena_layout(h->npad, h->symmetric, h->sorted, h->n);
 
     const int nlocal = multi_dev ? cfg->ngpus : 1;
     h->shards.resize(nlocal);
@@ -793,15 +1069,17 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
         NB_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
         NB_CUDA(cudaEventCreate(&s.ev0));
         NB_CUDA(cudaEventCreate(&s.ev1));
-        const size_t bytes = sizeof(double2) * static_cast<size_t>(h->npad);
-        NB_CUDA(cudaMalloc(&s.pos[0], bytes));
-        NB_CUDA(cudaMalloc(&s.pos[1], bytes));
+        NB_CUDA(cudaEventCreateWithFlags(&s.ev_copy, cudaEventDisableTiming));
+        NB_CUDA(cudaMalloc(&s.arena, h->lay.bytes));
+        NB_CUDA(cudaMemsetAsync(s.arena, 0, h->lay.bytes, s.stream));
+        point_into_arena(h->lay, s.arena, &s.pos[0], &s.pos[1], &s.vel, &s.frc, &s.vbuf, &s.boxes, &s.flags);
+        s.epoch = reinterpret_cast<unsigned long long *>(s.arena + h->lay.epoch);
+        if (!h->symmetric) s.vbuf = nullptr;
+        if (!h->sorted) s.boxes = nullptr;
         NB_CUDA(cudaMalloc(&s.mr, bytes));
-        NB_CUDA(cudaMalloc(&s.vel, bytes));
-        NB_CUDA(cudaMalloc(&s.frc, bytes));
-        NB_CUDA(cudaMemsetAsync(s.pos[1], 0, bytes, s.stream));
-        NB_CUDA(cudaMemsetAsync(s.frc, 0, bytes, s.stream));
-        if (cfg->mode == NBODY_GPU_MODE_FAST) {
+        NB_CUDA(cudaMemsetAsync(s.mr, 0, bytes, s.stream));
+        NB_CUDA(cudaMalloc(&s.plan, sizeof(double) * 6 * static_cast<size_t>(h->npad)));
+        if (fast) {
             NB_CUDA(cudaMalloc(&s.part, bytes * h->nsplit));
             NB_CUDA(cudaMemsetAsync(s.part, 0, bytes * h->nsplit, s.stream));
             if (h->symmetric) {
@@ -813,13 +1091,8 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
                 s.nblocks_owned = static_cast<int>(slots);
                 NB_CUDA(cudaMalloc(&s.colpart, bytes * slots));
                 NB_CUDA(cudaMemsetAsync(s.colpart, 0, bytes * slots, s.stream));
-                NB_CUDA(cudaMalloc(&s.sym_counter, sizeof(int)));
-                NB_CUDA(cudaMalloc(&s.vbuf, bytes * SYM_V));
-                NB_CUDA(cudaMemsetAsync(s.vbuf, 0, bytes * SYM_V, s.stream));
             }
             if (h->sorted) {
-                const size_t ntiles = static_cast<size_t>((h->n + TILE_J - 1) / TILE_J);
-                NB_CUDA(cudaMalloc(&s.boxes, ntiles * SYM_BOX_DOUBLES * sizeof(double)));
                 NB_CUDA(cudaMalloc(&s.orig, sizeof(int) * static_cast<size_t>(h->npad)));
                 NB_CUDA(cudaMalloc(&s.orig_tmp, sizeof(int) * static_cast<size_t>(h->npad)));
                 NB_CUDA(cudaMalloc(&s.mr0, bytes));
@@ -833,7 +1106,6 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
             }
         }
     }
-    NB_CUDA(cudaMallocHost(&h->stage, sizeof(double2) * static_cast<size_t>(h->npad) * NSTAGE_BUF));
 
     if (h->sharded) {
         const char *why = "";
@@ -852,24 +1124,24 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
             for (int k = 0; k < nlocal; ++k) h->shards[k].comm = comms[k];
         }
     }
+    int rc = NBODY_GPU_OK;
+    if (h->sharded && h->symmetric && cfg->p2p >= 0) {
+        rc = setup_p2p(h);
+        if (!rc && !h->p2p && cfg->p2p > 0) rc = fail(NBODY_GPU_ECUDA, "peer-memory exchange requested but peer access is unavailable");
+        if (rc) return rc;
+    }
 
-    int rc = upload(h, nullptr, 0, x, y, 0);
-    if (!rc) rc = upload(h, &Shard::mr, 0, mass, radius, 1);
-    if (!rc) rc = upload(h, &Shard::vel, 0, xv, yv, 2);
     h->cur = 0;
+    rc = upload_state(h, 0, x, y, xv, yv, mass, radius);
     if (!rc && h->sorted) {
         for (Shard &s : h->shards) {
             NB_CUDA(cudaSetDevice(s.device));
-            NB_CUDA(cudaMemcpyAsync(s.mr0, s.mr, sizeof(double2) * static_cast<size_t>(h->npad), cudaMemcpyDeviceToDevice, s.stream));
+            NB_CUDA(cudaMemcpyAsync(s.mr0, s.mr, bytes, cudaMemcpyDeviceToDevice, s.stream));
             launch_iota(s.orig, h->npad, s.stream);
         }
         rc = resort(h, false);
     }
-    if (!rc && h->sharded && h->symmetric && cfg->p2p >= 0) {
-        rc = setup_p2p(h);
-        if (!rc && !h->p2p && cfg->p2p > 0) rc = fail(NBODY_GPU_ECUDA, "peer-memory exchange requested but peer access is unavailable");
-    }
-    if (!rc) rc = sync_all(h);   // the staging buffers are free again
+    if (!rc) rc = sync_all(h);
     return rc;
 }
 
@@ -900,43 +1172,44 @@ int nbody_gpu_init(nbody_gpu **out, const nbody_gpu_cfg *cfg, const double *x, c
 
 int nbody_gpu_set_state(nbody_gpu *h, const double *x, const double *y, const double *xv, const double *yv)
 {
-    if (!h || !x || !y || !xv || !yv) return fail(NBODY_GPU_EINVAL, "NULL argument");
-    int rc = sync_all(h);
-    if (!rc) rc = upload(h, nullptr, h->cur, x, y, 0);
-    if (!rc) rc = upload(h, &Shard::vel, 0, xv, yv, 1);
+    int rc = check_usable(h);
     if (rc) return rc;
-    for (Shard &s : h->shards) {
-        NB_CUDA(cudaSetDevice(s.device));
-        NB_CUDA(cudaMemsetAsync(s.frc, 0, sizeof(double2) * static_cast<size_t>(h->npad), s.stream));
-        if (h->sorted) {   // the upload is in original order: back to the identity permutation, then sort again
+    if (!x || !y || !xv || !yv) return fail(NBODY_GPU_EINVAL, "NULL argument");
+    rc = upload_state(h, h->cur, x, y, xv, yv, nullptr, nullptr);
+    if (rc) return poison(h, rc);
+    if (h->sorted) {   // the upload is in original order: back to the identity permutation, then sort again
+        for (Shard &s : h->shards) {
+            NB_CUDA(cudaSetDevice(s.device));
             NB_CUDA(cudaMemcpyAsync(s.mr, s.mr0, sizeof(double2) * static_cast<size_t>(h->npad), cudaMemcpyDeviceToDevice, s.stream));
             launch_iota(s.orig, h->npad, s.stream);
+            h->launches[2] += 1;
         }
-    }
-    if (h->sorted) {
         rc = resort(h, false);
-        if (rc) return rc;
+        if (rc) return poison(h, rc);
     }
-    return sync_all(h);   // the staging buffers are free again; no device runs ahead into a step
+    return NBODY_GPU_OK;   // the host buffers are free again; the sort may still be queued
 }
 
 int nbody_gpu_step(nbody_gpu *h, int steps)
 {
-    if (!h) return fail(NBODY_GPU_EINVAL, "handle is NULL");
-    return do_steps(h, steps);
+    int rc = check_usable(h);
+    if (rc) return rc;
+    return poison(h, do_steps(h, steps));
 }
 
 int nbody_gpu_step_timed(nbody_gpu *h, int steps, float *ms)
 {
-    if (!h || !ms) return fail(NBODY_GPU_EINVAL, "NULL argument");
-    int rc = sync_all(h);
+    int rc = check_usable(h);
     if (rc) return rc;
+    if (!ms) return fail(NBODY_GPU_EINVAL, "NULL argument");
+    rc = sync_all(h);
+    if (rc) return poison(h, rc);
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
         NB_CUDA(cudaEventRecord(s.ev0, s.stream));
     }
     rc = do_steps(h, steps);
-    if (rc) return rc;
+    if (rc) return poison(h, rc);
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
         NB_CUDA(cudaEventRecord(s.ev1, s.stream));
@@ -949,6 +1222,8 @@ int nbody_gpu_step_timed(nbody_gpu *h, int steps, float *ms)
         NB_CUDA(cudaEventElapsedTime(&t, s.ev0, s.ev1));
         if (t > worst) worst = t;
     }
+    rc = sync_all(h);   // also reads the peer-exchange error word
+    if (rc) return poison(h, rc);
     *ms = worst;
     return NBODY_GPU_OK;
 }
@@ -956,10 +1231,9 @@ int nbody_gpu_step_timed(nbody_gpu *h, int steps, float *ms)
 namespace {
 struct EventMarks : StepMarks {
     nbody_gpu *h;
-    std::vector<cudaEvent_t> ev;   // [shard][step][phase 0..5]
-    int steps, step = 0;
-    EventMarks(nbody_gpu *h_, int steps_) : h(h_), ev(h_->shards.size() * static_cast<size_t>(steps_) * 6, nullptr), steps(steps_) {}
-    cudaEvent_t &at(size_t k, int st, int phase) { return ev[(k * steps + st) * 6 + phase]; }
+    int step = 0;   // index inside the current pass, < PROF_CHUNK
+    explicit EventMarks(nbody_gpu *h_) : h(h_) {}
+    cudaEvent_t &at(size_t k, int st, int phase) { return h->shards[k].prof_ev[static_cast<size_t>(st) * 6 + phase]; }
     int mark(size_t k, int phase) override
     {
         NB_CUDA(cudaSetDevice(h->shards[k].device));
@@ -967,23 +1241,14 @@ struct EventMarks : StepMarks {
         return NBODY_GPU_OK;
     }
 };
-}  // namespace
 
-int nbody_gpu_step_profiled(nbody_gpu *h, int steps, int flush_l2, float out_ms[4])
+int profiled_pass(nbody_gpu *h, int steps, int flush_l2, float acc_out[4])
 {
-    if (!h || !out_ms || steps < 0) return fail(NBODY_GPU_EINVAL, "bad argument");
-    int rc = sync_all(h);
-    if (rc) return rc;
-    for (int q = 0; q < 4; ++q) out_ms[q] = 0.f;
-    if (steps == 0) return NBODY_GPU_OK;
     const size_t flush_bytes = 256u << 20;
     const size_t nsh = h->shards.size();
-    EventMarks marks(h, steps);
+    EventMarks marks(h);
     for (size_t k = 0; k < nsh; ++k) {
         NB_CUDA(cudaSetDevice(h->shards[k].device));
-        for (int st = 0; st < steps; ++st)
-            for (int ph = 0; ph < 6; ++ph) NB_CUDA(cudaEventCreate(&marks.at(k, st, ph)));
-        if (flush_l2 && !h->shards[k].flush) NB_CUDA(cudaMalloc(&h->shards[k].flush, flush_bytes));   // first call only
         NB_CUDA(cudaEventRecord(h->shards[k].ev0, h->shards[k].stream));
     }
     for (int st = 0; st < steps; ++st) {
@@ -994,133 +1259,155 @@ int nbody_gpu_step_profiled(nbody_gpu *h, int steps, int flush_l2, float out_ms[
             }
         }
         marks.step = st;
-        rc = run_one_step(h, &marks);
+        int rc = run_one_step(h, &marks);
         if (rc) return rc;
     }
     for (size_t k = 0; k < nsh; ++k) {
         NB_CUDA(cudaSetDevice(h->shards[k].device));
         NB_CUDA(cudaEventRecord(h->shards[k].ev1, h->shards[k].stream));
     }
+    float worst[4] = {0.f, 0.f, 0.f, 0.f};
     for (size_t k = 0; k < nsh; ++k) {
         Shard &s = h->shards[k];
         NB_CUDA(cudaSetDevice(s.device));
         NB_CUDA(cudaEventSynchronize(s.ev1));
         float acc[4] = {0.f, 0.f, 0.f, 0.f}, t = 0.f;
         NB_CUDA(cudaEventElapsedTime(&acc[0], s.ev0, s.ev1));
-        if (getenv("NBODY_PROFILE_SPLIT")) {   // development knob: per-step phase times of this shard
-            for (int st = 0; st < steps; ++st) {
-                float ph_ms[5];
-                for (int ph = 0; ph < 5; ++ph) NB_CUDA(cudaEventElapsedTime(&ph_ms[ph], marks.at(k, st, ph), marks.at(k, st, ph + 1)));
-                fprintf(stderr, "[nbody_gpu] shard %d step %d: force %.3f fold %.3f exchA %.3f integrate %.3f exchB %.3f ms\n",
-                        s.part_index, st, ph_ms[0], ph_ms[1], ph_ms[2], ph_ms[3], ph_ms[4]);
-            }
-        }
         for (int st = 0; st < steps; ++st) {
             // phases: 0-1 force kernel | 1-2 symmetric fold | 2-3 exchange A | 3-4 integrate | 4-5 exchange B
             static const int bucket[5] = {1, 2, 3, 2, 3};
+            float ph_ms[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
             for (int ph = 0; ph < 5; ++ph) {
                 NB_CUDA(cudaEventElapsedTime(&t, marks.at(k, st, ph), marks.at(k, st, ph + 1)));
-                acc[bucket[ph]] += t;
+                ph_ms[ph] = t;
             }
+            for (int ph = 0; ph < 5; ++ph) acc[bucket[ph]] += ph_ms[ph];
+#ifdef NBODY_DEV
+            if (getenv("NBODY_PROFILE_SPLIT"))   // development knob: per-step phase times of this shard
+                fprintf(stderr, "[nbody_gpu] shard %d step %d: force %.3f fold %.3f exchA %.3f integrate %.3f exchB %.3f ms\n",
+                        s.part_index, st, ph_ms[0], ph_ms[1], ph_ms[2], ph_ms[3], ph_ms[4]);
+#endif
         }
         if (!h->sharded) acc[3] = 0.f;
         for (int q = 0; q < 4; ++q)
-            if (acc[q] > out_ms[q]) out_ms[q] = acc[q];
-        for (int st = 0; st < steps; ++st)
-            for (int ph = 0; ph < 6; ++ph) cudaEventDestroy(marks.at(k, st, ph));
-        NB_CUDA(cudaGetLastError());
+            if (acc[q] > worst[q]) worst[q] = acc[q];
     }
+    for (int q = 0; q < 4; ++q) acc_out[q] += worst[q];
+    return NBODY_GPU_OK;
+}
+}  // namespace
+
+int nbody_gpu_step_profiled(nbody_gpu *h, int steps, int flush_l2, float out_ms[4])
+{
+    int rc = check_usable(h);
+    if (rc) return rc;
+    if (!out_ms || steps < 0) return fail(NBODY_GPU_EINVAL, "bad argument");
+    rc = sync_all(h);
+    if (rc) return poison(h, rc);
+    for (int q = 0; q < 4; ++q) out_ms[q] = 0.f;
+    for (Shard &s : h->shards) {   // first call only: the event pool and the flush scratch stay with the handle
+        NB_CUDA(cudaSetDevice(s.device));
+        if (s.prof_ev.empty()) {
+            s.prof_ev.assign(static_cast<size_t>(PROF_CHUNK) * 6, nullptr);
+            for (cudaEvent_t &e : s.prof_ev) NB_CUDA(cudaEventCreate(&e));
+        }
+        if (flush_l2 && !s.flush) NB_CUDA(cudaMalloc(&s.flush, 256u << 20));
+    }
+    // bounded passes: a fixed pool of events however long the run (nbody-par --measure-comm passes the whole run)
+    for (int done = 0; done < steps;) {
+        const int pass = steps - done < PROF_CHUNK ? steps - done : PROF_CHUNK;
+        rc = profiled_pass(h, pass, flush_l2, out_ms);
+        if (rc) return poison(h, rc);
+        done += pass;
+    }
+    rc = sync_all(h);
+    if (rc) return poison(h, rc);
     return NBODY_GPU_OK;
 }
 
 int nbody_gpu_sync(nbody_gpu *h)
 {
-    if (!h) return fail(NBODY_GPU_EINVAL, "handle is NULL");
-    return sync_all(h);
+    int rc = check_usable(h);
+    if (rc) return rc;
+    return poison(h, sync_all(h));
 }
 
-// Device array of shard 0 -> pinned staging buffer `buf` (asynchronous), in the caller's body order: cell order
-// is undone on the device first.  download_finish de-interleaves after the stream has been synchronised.
-static int download_begin(nbody_gpu *h, const double2 *src, int buf, bool wanted)
+// Up to three double2 device arrays of shard 0 (slot order) -> the caller's planar arrays (body order): one
+// gather kernel writes planar staging on the device, then one D2H copy per requested array, straight into the
+// caller's memory (full PCIe speed if it is registered, driver-staged if pageable).
+static int download(nbody_gpu *h, const double2 *const src[3], double *const out[6])
 {
-    if (!wanted) return NBODY_GPU_OK;
     Shard &s = h->shards[0];
-    if (h->sorted) {
-        launch_unsort(src, s.orig, s.gat[buf], h->n, s.stream);
-        src = s.gat[buf];
+    NB_CUDA(cudaSetDevice(s.device));
+    const size_t np = static_cast<size_t>(h->npad);
+    GatherArgs g;
+    bool any = false;
+    for (int k = 0; k < 3; ++k) {
+        const bool want = out[2 * k] || out[2 * k + 1];
+        g.src[k] = want ? src[k] : nullptr;
+        g.a[k] = s.plan + (2 * k) * np;
+        g.b[k] = s.plan + (2 * k + 1) * np;
+        any |= want;
     }
-    NB_CUDA(cudaMemcpyAsync(h->stage + static_cast<size_t>(buf) * h->npad, src, sizeof(double2) * static_cast<size_t>(h->n),
-                            cudaMemcpyDeviceToHost, s.stream));
+    if (!any) return NBODY_GPU_OK;
+    g.orig = h->sorted ? s.orig : nullptr;
+    g.n = h->n;
+    launch_gather_planar(g, s.stream);
+    h->launches[2] += 1;
+    for (int k = 0; k < 6; ++k)
+        if (out[k]) NB_CUDA(cudaMemcpyAsync(out[k], s.plan + k * np, sizeof(double) * h->n, cudaMemcpyDeviceToHost, s.stream));
     return NBODY_GPU_OK;
-}
-
-static void download_finish(nbody_gpu *h, int buf, double *a, double *b)
-{
-    const double2 *stage = h->stage + static_cast<size_t>(buf) * h->npad;
-    if (a && b) {
-        for (int i = 0; i < h->n; ++i) {
-            a[i] = stage[i].x;
-            b[i] = stage[i].y;
-        }
-    } else if (a) {
-        for (int i = 0; i < h->n; ++i) a[i] = stage[i].x;
-    } else if (b) {
-        for (int i = 0; i < h->n; ++i) b[i] = stage[i].y;
-    }
 }
 
 int nbody_gpu_forces(nbody_gpu *h, double *xf, double *yf)
 {
-    if (!h) return fail(NBODY_GPU_EINVAL, "handle is NULL");
+    int rc = check_usable(h);
+    if (rc) return rc;
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
-        enqueue_forces(h, s, h->cur);
-        if (h->symmetric) enqueue_sym_reduce(h, s);
-        h->launches[0] += 1;
+        if (!s.fscratch) {
+            NB_CUDA(cudaMalloc(&s.fscratch, sizeof(double2) * static_cast<size_t>(h->npad)));
+            NB_CUDA(cudaMemsetAsync(s.fscratch, 0, sizeof(double2) * static_cast<size_t>(h->npad), s.stream));
+        }
+        rc = enqueue_forces(h, s, h->cur, s.fscratch);
+        if (rc) return poison(h, rc);
+        if (h->symmetric) enqueue_sym_reduce(h, s, false);
         NB_CUDA(cudaGetLastError());
     }
-    int rc = NBODY_GPU_OK;
-    if (h->symmetric) rc = allgather(h, AG_VBUF);
-    if (rc) return rc;
+    if (h->symmetric && h->sharded) rc = allgather(h, AG_VBUF);
+    if (rc) return poison(h, rc);
     if (h->cfg.mode == NBODY_GPU_MODE_FAST) {
         for (Shard &s : h->shards) {
             NB_CUDA(cudaSetDevice(s.device));
-            launch_reduce_fast(integrate_args(h, s, h->cur), s.stream);   // partial sums -> frc
+            IntegrateArgs a = integrate_args(h, s, h->cur);
+            a.frc = s.fscratch;   // the last step's forces in frc stay what print() shows
+            launch_reduce_fast(a, s.stream);   // partial sums -> fscratch
             h->launches[2] += 1;
         }
     }
-    if (!h->symmetric || h->p2p) rc = allgather(h, AG_FRC);
-    if (rc) return rc;
-    Shard &s0 = h->shards[0];
-    NB_CUDA(cudaSetDevice(s0.device));
-    rc = download_begin(h, s0.frc, 0, xf || yf);
+    if (state_sharded(h)) rc = allgather(h, AG_SCRATCH);
+    if (rc) return poison(h, rc);
+    const double2 *src[3] = {nullptr, h->shards[0].fscratch, nullptr};
+    double *out[6] = {nullptr, nullptr, xf, yf, nullptr, nullptr};
+    rc = download(h, src, out);
     if (!rc) rc = sync_all(h);
-    if (rc) return rc;
-    download_finish(h, 0, xf, yf);
-    return NBODY_GPU_OK;
+    return poison(h, rc);
 }
 
 int nbody_gpu_fetch(nbody_gpu *h, double *x, double *y, double *xf, double *yf, double *xv, double *yv)
 {
-    if (!h) return fail(NBODY_GPU_EINVAL, "handle is NULL");
-    int rc = NBODY_GPU_OK;
-    if (h->sharded && (!h->symmetric || h->p2p)) {
-        // forces and velocities live sharded during the run; gather them like the reference's
-        // whole-struct MPI_Allgatherv leaves them (nbody-par.c:933-936)
-        if (xv || yv) rc = allgather(h, AG_VEL);
-        if (!rc && (xf || yf)) rc = allgather(h, AG_FRC);
-        if (rc) return rc;
-    }
-    Shard &s0 = h->shards[0];
-    NB_CUDA(cudaSetDevice(s0.device));
-    rc = download_begin(h, s0.pos[h->cur], 0, x || y);
-    if (!rc) rc = download_begin(h, s0.frc, 1, xf || yf);
-    if (!rc) rc = download_begin(h, s0.vel, 2, xv || yv);
-    if (!rc) rc = sync_all(h);
+    int rc = check_usable(h);
     if (rc) return rc;
-    download_finish(h, 0, x, y);
-    download_finish(h, 1, xf, yf);
-    download_finish(h, 2, xv, yv);
+    // forces and velocities live sharded during the run; complete them like the reference's
+    // whole-struct MPI_Allgatherv leaves them (nbody-par.c:933-936)
+    rc = complete_state(h, xv || yv, xf || yf);
+    if (rc) return poison(h, rc);
+    Shard &s0 = h->shards[0];
+    const double2 *src[3] = {s0.pos[h->cur], s0.frc, s0.vel};
+    double *out[6] = {x, y, xf, yf, xv, yv};
+    rc = download(h, src, out);
+    if (!rc) rc = sync_all(h);
+    if (rc) return poison(h, rc);
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
         NB_CUDA(cudaGetLastError());
@@ -1132,20 +1419,26 @@ int nbody_gpu_describe(const nbody_gpu *h, char *buf, int len)
 {
     if (!h) return 0;
     const bool fast = h->cfg.mode == NBODY_GPU_MODE_FAST;
-    const char *kernel = !fast ? "forces_kernel<EXACT>" : h->symmetric ? (h->n >= SYM_WIDE_N ? "forces_sym_kernel<64,8>" : "forces_sym_kernel<128,4>") : "forces_fast_kernel<2,4,1,true>";
+    const char *kernel = !fast ? (h->small ? "small_world_kernel" : "forces_exact_wide_kernel")
+                         : h->symmetric ? (h->n >= SYM_WIDE_N ? "forces_sym_kernel<64,8>" : "forces_sym_kernel<128,4>")
+                                        : "forces_fast_kernel<2,4,1,true>";
     // FP64-pipe instructions per directed pair-interaction (SASS counts): the symmetric
-    // kernel issues 19 per unordered pair = 2 interactions; exact mode is not a fixed count (divisions, branches)
-    // (19 near, 17 in far-field tiles: see nbody_gpu_far_fraction)
+    // kernel issues 19 per unordered pair = 2 interactions (17 in far-field tiles: see nbody_gpu_far_fraction);
+    // exact mode is not a fixed count (divisions, branches)
     const double ipp = !fast ? 0.0 : h->symmetric ? 9.5 : 16.0;
-    char tmp[640];
+    const int graph = h->small ? 0 : ((!h->sharded || h->p2p) ? h->graph_steps : 0);
+    char tmp[768];
     const int need = snprintf(tmp, sizeof tmp,
                               "{\"mode\": \"%s\", \"kernel\": \"%s\", \"symmetric\": %s, \"nsplit\": %d, \"chunk\": %d, "
-                              "\"row_blocks\": %d, \"shards\": %d, \"graph_steps\": %d, \"exchange\": \"%s\", \"fp64_instr_per_pair\": %.1f, "
-                              "\"cell_order\": %s, \"sort_interval\": %d, \"sorts\": %lld}",
-                              fast ? "fast" : "exact", kernel, h->symmetric ? "true" : "false", h->nsplit, h->chunk,
-                              h->symmetric ? h->nblocks : 0, h->nshards_total, h->sharded ? 0 : h->graph_steps,
-                              !h->sharded ? "none" : h->p2p ? "peer-memory stores + signal/wait kernels" : "ncclAllGather", ipp,
-                              h->sorted ? "true" : "false", h->sorted ? h->sort_interval : 0, h->sorts);
+                              "\"short_chunks\": %d, \"row_blocks\": %d, \"shards\": %d, \"graph_steps\": %d, \"single_launch_loop\": %s, "
+                              "\"exchange\": \"%s\", \"fp64_instr_per_pair\": %.1f, "
+                              "\"cell_order\": %s, \"fused_tile_boxes\": %s, \"sort_interval\": %d, \"sorts\": %lld}",
+                              fast ? "fast" : "exact", kernel, h->symmetric ? "true" : "false", h->nsplit,
+                              h->symmetric ? h->cm.chunk : h->chunk, h->symmetric ? h->cm.nsplit - h->cm.nbig : 0,
+                              h->symmetric ? h->nblocks : 0, h->nshards_total, graph, h->small ? "true" : "false",
+                              !h->sharded ? "none" : h->p2p ? "peer-memory stores + barrier kernels" : "ncclAllGather", ipp,
+                              h->sorted ? "true" : "false", h->fused_boxes ? "true" : "false",
+                              h->sorted ? h->sort_interval : 0, h->sorts);
     if (buf && len > 0) {
         strncpy(buf, tmp, static_cast<size_t>(len) - 1);
         buf[len - 1] = 0;
@@ -1155,23 +1448,26 @@ int nbody_gpu_describe(const nbody_gpu *h, char *buf, int len)
 
 int nbody_gpu_far_fraction(nbody_gpu *h, double *fraction)
 {
-    if (!h || !fraction) return fail(NBODY_GPU_EINVAL, "NULL argument");
+    int rc = check_usable(h);
+    if (rc) return rc;
+    if (!fraction) return fail(NBODY_GPU_EINVAL, "NULL argument");
     *fraction = 0.0;
     if (!h->sorted) return NBODY_GPU_OK;
-    int rc = sync_all(h);
-    if (rc) return rc;
+    rc = sync_all(h);
+    if (rc) return poison(h, rc);
     Shard &s = h->shards[0];
     NB_CUDA(cudaSetDevice(s.device));
     const int ntiles = (h->n + TILE_J - 1) / TILE_J;
     std::vector<double> bx(static_cast<size_t>(ntiles) * SYM_BOX_DOUBLES);
-    launch_tile_boxes(s.pos[h->cur], s.mr, h->n, s.boxes, s.stream);
+    // the boxes always describe pos[cur] (re-sort, integrate_kernel): read them as the force kernel would
+    if (!h->fused_boxes) launch_tile_boxes(s.pos[h->cur], s.mr, h->n, s.boxes, s.stream);
     NB_CUDA(cudaMemcpyAsync(bx.data(), s.boxes, bx.size() * sizeof(double), cudaMemcpyDeviceToHost, s.stream));
     NB_CUDA(cudaStreamSynchronize(s.stream));
     // the same walk and the same test as forces_sym_kernel: tiles above each row block
     const int tiles_per_block = SYM_RB / TILE_J;
     double far = 0.0, all = 0.0;
     for (int B = 0; B < h->nblocks; ++B) {
-        double b[5];
+        double b[5] = {0, 0, 0, 0, 0};
         for (int t = 0; t < tiles_per_block && B * tiles_per_block + t < ntiles; ++t) {
             const double *q = &bx[static_cast<size_t>(B * tiles_per_block + t) * SYM_BOX_DOUBLES];
             if (t == 0) { for (int k = 0; k < 5; ++k) b[k] = q[k]; continue; }
@@ -1197,27 +1493,25 @@ int nbody_gpu_far_fraction(nbody_gpu *h, double *fraction)
 
 int nbody_gpu_render(nbody_gpu *h, unsigned char *rgb)
 {
-    if (!h || !rgb) return fail(NBODY_GPU_EINVAL, "NULL argument");
+    int rc = check_usable(h);
+    if (rc) return rc;
+    if (!rgb) return fail(NBODY_GPU_EINVAL, "NULL argument");
     Shard &s = h->shards[0];   // every device holds all current positions
     NB_CUDA(cudaSetDevice(s.device));
     const size_t npix = static_cast<size_t>(h->cfg.xdim) * h->cfg.ydim;
-    int *owner = nullptr;
-    unsigned char *img = nullptr;
-    NB_CUDA(cudaMalloc(&owner, npix * sizeof(int)));
-    NB_CUDA(cudaMalloc(&img, npix * 3));
+    if (!s.render_owner) NB_CUDA(cudaMalloc(&s.render_owner, npix * sizeof(int)));   // first call only
+    if (!s.render_img) NB_CUDA(cudaMalloc(&s.render_img, npix * 3));
     const double2 *rpos = s.pos[h->cur], *rmr = s.mr;
     if (h->sorted) {   // the lowest ORIGINAL index wins a pixel (nbody-seq.c:336-347): paint from body order
         launch_unsort(s.pos[h->cur], s.orig, s.gat[0], h->n, s.stream);
         rpos = s.gat[0];
         rmr = s.mr0;
     }
-    launch_render(rpos, rmr, h->n, h->cfg.xdim, h->cfg.ydim, owner, img, s.stream);
+    launch_render(rpos, rmr, h->n, h->cfg.xdim, h->cfg.ydim, s.render_owner, s.render_img, s.stream);
     h->launches[2] += 3;
-    cudaError_t e = cudaMemcpyAsync(rgb, img, npix * 3, cudaMemcpyDeviceToHost, s.stream);
+    cudaError_t e = cudaMemcpyAsync(rgb, s.render_img, npix * 3, cudaMemcpyDeviceToHost, s.stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
-    cudaFree(owner);
-    cudaFree(img);
-    if (e != cudaSuccess) return fail(NBODY_GPU_ECUDA, "render failed: %s", cudaGetErrorString(e));
+    if (e != cudaSuccess) return poison(h, fail(NBODY_GPU_ECUDA, "render failed: %s", cudaGetErrorString(e)));
     return NBODY_GPU_OK;
 }
 

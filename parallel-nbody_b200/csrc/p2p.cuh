@@ -5,12 +5,14 @@
 // reach everybody (the reference: one MPI_Allgatherv of whole structs, nbody-par.c:913-917).  Here both
 // are plain stores into peer memory issued by the producing kernels themselves:
 //   sym_reduce_p2p_kernel  writes vbuf[v][j] straight into the vbuf of the GPU that owns row j,
-//   integrate_kernel       writes pos_new[i] into every GPU's position buffer,
-// each followed by a one-warp signal kernel (release store of the step's epoch into every peer's flag
-// word) and, on the consumer side, a one-warp wait kernel (acquire loads until all P flags carry the
-// epoch).  Positions are double-buffered and the two waits order the reuse of vbuf, so no buffer is
-// overwritten while a peer still reads it.  A wait gives up after ~10 s and
-// raises an error word instead of hanging the GPU.
+//   integrate_kernel       writes pos_new[i] (and the tile boxes) into every GPU's buffers,
+// each followed by a one-warp barrier kernel: release store of this device's barrier count into every peer's
+// flag word, then acquire loads until all P flags carry that count.  The count lives in device memory
+// (PeerTable::epoch) and is advanced by the kernel itself, so the launch arguments never change and the whole
+// sharded step loop can sit in a CUDA graph.  Positions are double-buffered and the two barriers order the
+// reuse of vbuf, so no buffer is overwritten while a peer still reads it.
+// A wait gives up after ~10 s, raises an error word and poisons every peer's flags so that the other GPUs stop
+// at once instead of waiting out their own 10 s.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -18,31 +20,43 @@
 
 namespace nbody {
 
-__global__ void p2p_signal_kernel(const PeerTable t, int phase, unsigned long long epoch)
+constexpr unsigned long long P2P_POISON = ~0ULL;
+
+__global__ void __launch_bounds__(32) p2p_barrier_kernel(const PeerTable t, int phase, int *error_word)
 {
     const int r = threadIdx.x;
+    unsigned long long e = 0;
+    if (r == 0) {
+        e = t.epoch[phase] + 1;   // this device's own count: same sequence of barriers on every device
+        t.epoch[phase] = e;
+    }
+    e = __shfl_sync(0xffffffffu, e, 0);
     if (r >= t.npeers) return;
+    if (*reinterpret_cast<volatile int *>(error_word) != 0) return;   // an earlier wait already gave up
+    // signal: everything this device stored before this kernel (stream order) is visible to a peer that sees e
     __threadfence_system();
     unsigned long long *dst = t.flags[r] + phase * MAX_PEERS + t.me;
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(epoch) : "memory");
-}
-
-__global__ void p2p_wait_kernel(const PeerTable t, int phase, unsigned long long epoch, int *error_word)
-{
-    const int r = threadIdx.x;
-    if (r >= t.npeers) return;
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(e) : "memory");
+    // wait for peer r's signal
     const unsigned long long *src = t.flags[t.me] + phase * MAX_PEERS + r;
     const long long t0 = clock64();
     unsigned long long v = 0;
-    if (*reinterpret_cast<volatile int *>(error_word) != 0) return;   // an earlier wait already gave up
     for (;;) {
         asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(src) : "memory");
-        if (v >= epoch) break;
+        if (v >= e) break;
         if (clock64() - t0 > 20000000000LL) {   // ~10 s at 1.9 GHz: a peer never arrived
-            atomicExch(error_word, 1 + phase);
+            v = P2P_POISON;
             break;
         }
         __nanosleep(200);
+    }
+    if (v == P2P_POISON) {
+        atomicExch(error_word, 1 + phase);
+        for (int q = 0; q < t.npeers; ++q)       // release everybody who waits for this device, in every phase
+            for (int ph = 0; ph < P2P_PHASES; ++ph) {
+                unsigned long long *d = t.flags[q] + ph * MAX_PEERS + t.me;
+                asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(d), "l"(P2P_POISON) : "memory");
+            }
     }
 }
 
@@ -66,7 +80,7 @@ __global__ void __launch_bounds__(128) sym_reduce_p2p_kernel(const SymReduceArgs
         }
     }
     if (sym_vrank(blk) == v) {
-        for (int s = (blk * SYM_RB) / a.chunk; s < a.nsplit; ++s) {
+        for (int s = chunk_of(a.cm, blk * SYM_RB); s < a.cm.nsplit; ++s) {
             const double2 c = a.rowpart[static_cast<size_t>(s) * a.npad + j];
             xf += c.x;
             yf += c.y;

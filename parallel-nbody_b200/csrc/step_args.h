@@ -26,6 +26,29 @@ constexpr int SYM_RB = 512;         // rows per block of the symmetric (evaluate
 constexpr int SYM_WIDE_N = 131072;  // from this many bodies on: 64 threads x 8 bodies per CTA instead of 128 x 4
 constexpr int SYM_BOX_DOUBLES = 8;  // per-tile bounding box: xmin ymin xmax ymax rmax + padding (one 64-byte bulk copy)
 
+// j-chunks of the symmetric kernel: `nbig` chunks of `chunk` bodies cover [0, jsmall0), then chunks of `csmall`
+// bodies (one tile) cover [jsmall0, n).  A CTA is one (row block, chunk) item and the hardware dispatches CTAs in
+// chunk order, so the short items come last: when the long items run out, every SM slot that falls idle picks
+// up a quarter-size item instead of waiting for the slowest long one (the tail of a launch costs about half an
+// item per slot: 3.4 % of the step on an 8-way shard of N = 262144 with uniform chunks).  The map is a function
+// of n only, like everything else that fixes the summation order.
+struct ChunkMap {
+    int chunk;     // long chunk length, a multiple of SYM_RB
+    int nbig;      // number of long chunks
+    int jsmall0;   // nbig * chunk: where the short chunks start (>= n if there are none)
+    int csmall;    // short chunk length (TILE_J)
+    int nsplit;    // chunks in total
+};
+__host__ __device__ inline int chunk_start(const ChunkMap &m, int s)
+{
+    return s < m.nbig ? s * m.chunk : m.jsmall0 + (s - m.nbig) * m.csmall;
+}
+__host__ __device__ inline int chunk_len(const ChunkMap &m, int s) { return s < m.nbig ? m.chunk : m.csmall; }
+__host__ __device__ inline int chunk_of(const ChunkMap &m, int j)
+{
+    return j < m.jsmall0 ? j / m.chunk : m.nbig + (j - m.jsmall0) / m.csmall;
+}
+
 struct SymArgs {
     const double2 *pos;
     const double2 *mr;
@@ -34,11 +57,8 @@ struct SymArgs {
     const double *boxes;  // [ceil(n/TILE_J)][8] per-tile bounding boxes (xmin ymin xmax ymax rmax . . .), or nullptr
     int n;
     int npad;
-    int chunk;            // j-chunk length, a multiple of SYM_RB
+    ChunkMap cm;
     int v0, nv;           // this device owns the row blocks B with (B % SYM_V) in [v0, v0+nv): "virtual ranks"
-    int *counter;         // persistent launch: work-item counter, zeroed before every launch (else nullptr)
-    int nitems;           // persistent launch: nblocks_here * nsplit
-    int nblocks_here, nsplit;
 };
 
 // The symmetric kernel's partial sums are combined through SYM_V fixed "virtual ranks": row block B
@@ -73,17 +93,23 @@ struct SymReduceArgs {
     const double2 *rowpart;
     const double2 *colpart;
     double2 *vbuf;        // [SYM_V][npad]
-    int n, npad, chunk, nsplit;
+    int n, npad;
+    ChunkMap cm;
     int v0, nv;
 };
 
 // Peer-memory view of a sharded job (all pointers are device addresses valid on THIS device: own memory,
 // cudaDeviceEnablePeerAccess mappings, or cudaIpcOpenMemHandle mappings).
 constexpr int MAX_PEERS = 8;
+constexpr int P2P_PHASES = 3;   // 0: force vectors (exchange A), 1: integrated positions (B), 2: uploaded / published state
 struct PeerTable {
     double2 *vbuf[MAX_PEERS];
     double2 *pos[2][MAX_PEERS];
-    unsigned long long *flags[MAX_PEERS];   // [2 phases][MAX_PEERS sources] epoch words on each device
+    double2 *vel[MAX_PEERS];
+    double2 *frc[MAX_PEERS];
+    double *boxes[MAX_PEERS];
+    unsigned long long *flags[MAX_PEERS];   // [P2P_PHASES][MAX_PEERS sources] epoch words on each device
+    unsigned long long *epoch;              // [P2P_PHASES] this device's own count of barriers passed per phase
     int npeers;                             // 0 = no peer exchange
     int me;
 };
@@ -98,10 +124,13 @@ struct IntegrateArgs {
     const double2 *vbuf;   // FAST symmetric: [SYM_V][npad] per-virtual-rank sums (see SymReduceArgs), else nullptr
     int nsplit;            // FAST: number of j-chunks
     int npad;
+    int n;                 // bodies
     int lo, hi;
     int xdim, ydim;
-    double2 *peer_pos_new[MAX_PEERS];   // fused position exchange: also store pos_new[i] here (npeers entries)
-    int npeers;                         // 0 = store to pos_new only
+    double2 *peer_pos_new[MAX_PEERS];   // fused position exchange: store pos_new[i] here instead (npeers entries)
+    double *boxes;                      // fused tile boxes of the NEW positions (cell order; lo % TILE_J == 0), or nullptr
+    double *peer_boxes[MAX_PEERS];      // with the fused exchange: every device's box array
+    int npeers;                         // 0 = store to pos_new / boxes only
 };
 
 // Cell order (kernels_sort.cu): key = Hilbert index of the position << 32 | original index, value = slot.
@@ -123,6 +152,25 @@ struct PermuteArgs {
     int *orig_out;
     int n;
 };
+// Planar host layout <-> the device's double2 arrays (kernels_sort.cu).
+struct ScatterArgs {                // uploaded rows [lo, hi) of planar (a, b) -> double2 array(s)
+    const double *a, *b;            // planar device staging, indexed by body
+    double2 *dst[MAX_PEERS];        // ndst destinations (this device, or every device of a peer-mapped job)
+    int ndst;
+    int lo, hi;
+};
+struct GatherArgs {                 // double2 arrays in slot order -> planar arrays in the caller's body order
+    const double2 *src[3];          // up to three arrays (nullptr = skip)
+    double *a[3], *b[3];
+    const int *orig;                // slot -> body (nullptr = identity)
+    int n;
+};
+struct PublishArgs {                // store this device's rows of up to two sharded arrays into every peer
+    const double2 *src[2];
+    double2 *dst[2][MAX_PEERS];
+    int npeers, me;
+    int lo, hi;
+};
 size_t sort_temp_bytes(int n);
 unsigned cell_key_host(double x, double y, double scale);
 int launch_sort(const SortArgs &a, cudaStream_t st);   // returns cudaError_t
@@ -130,19 +178,35 @@ void launch_permute(const PermuteArgs &a, cudaStream_t st);
 void launch_unsort(const double2 *in, const int *orig, double2 *out, int n, cudaStream_t st);
 void launch_iota(int *orig, int n, cudaStream_t st);
 void launch_tile_boxes(const double2 *pos, const double2 *mr, int n, double *boxes, cudaStream_t st);
+void launch_scatter(const ScatterArgs &a, cudaStream_t st);
+void launch_gather_planar(const GatherArgs &a, cudaStream_t st);
+void launch_publish(const PublishArgs &a, cudaStream_t st);
+
+// The whole step loop of a small world in ONE launch (smalln.cuh, EXACT mode).
+constexpr int SMALL_N_MAX = 256;    // bodies
+constexpr int SMALL_N_ONE_CTA = 32; // up to here one CTA; above, a cluster of SMALL_CLUSTER CTAs
+constexpr int SMALL_CLUSTER = 8;
+struct SmallArgs {
+    double2 *pos[2];      // ping-pong positions in HBM; `cur` holds the state at entry
+    const double2 *mr;
+    double2 *vel;
+    double2 *frc;
+    int n, steps, cur;
+    int xdim, ydim;
+};
+int launch_small_world(const SmallArgs &a, cudaStream_t st);   // returns cudaError_t
 
 // launchers, defined in kernels_exact.cu / kernels_fast.cu
-void launch_forces_exact(const ForceArgs &a, cudaStream_t st);
+int launch_forces_exact(const ForceArgs &a, cudaStream_t st);   // returns cudaError_t
 void launch_integrate_exact(const IntegrateArgs &a, cudaStream_t st);
 void launch_forces_fast(const ForceArgs &a, int nsplit, cudaStream_t st);
 void launch_integrate_fast(const IntegrateArgs &a, cudaStream_t st);
 void launch_reduce_fast(const IntegrateArgs &a, cudaStream_t st);
-int launch_forces_sym(SymArgs a, int nblocks_here, int nsplit, cudaStream_t st);   // returns cudaError_t
+int launch_forces_sym(const SymArgs &a, int nblocks_here, cudaStream_t st);   // returns cudaError_t
 void launch_render(const double2 *pos, const double2 *mr, int n, int xdim, int ydim, int *owner, unsigned char *rgb,
                    cudaStream_t st);
 void launch_sym_reduce(const SymReduceArgs &a, cudaStream_t st);
 void launch_sym_reduce_p2p(const SymReduceArgs &a, const PeerTable &t, int rows_per_shard, cudaStream_t st);
-void launch_p2p_signal(const PeerTable &t, int phase, unsigned long long epoch, cudaStream_t st);
-void launch_p2p_wait(const PeerTable &t, int phase, unsigned long long epoch, int *error_word, cudaStream_t st);
+void launch_p2p_barrier(const PeerTable &t, int phase, int *error_word, cudaStream_t st);
 
 }  // namespace nbody

@@ -15,6 +15,7 @@
 //   part[S][npad] double2          fast mode only: per-j-chunk partial sums
 #pragma once
 #include <cuda_runtime.h>
+#include <cfloat>
 #include <cstdint>
 
 #include "../../include/nbody_detmath.h"
@@ -191,13 +192,12 @@ __global__ void __launch_bounds__(FORCE_THREADS) forces_kernel(const ForceArgs a
 // ---------------------------------------------------------------------------------
 // integrate_kernel: one thread per owned body.
 // ---------------------------------------------------------------------------------
+// compute_velocities + compute_positions for one body (nbody-seq.c:114-165): p = position, q = (mass, radius),
+// v = velocity (updated in place), (xf, yf) = the body's pair-force sum; returns the new position.
 template <int MODE>
-__device__ __forceinline__ void integrate_body(const IntegrateArgs &a, int i, double xf, double yf,
-                                               const double *tab)
+__device__ __forceinline__ double2 integrate_math(double2 p, double2 q, double2 &v, double xf, double yf, int xdim,
+                                                  int ydim, const double *tab)
 {
-    const double2 p = a.pos_old[i];
-    const double2 q = a.mr[i];
-    double2 v = a.vel[i];
     if (MODE == MODE_EXACT) {
         // compute_velocities, nbody-seq.c:120-128
         double force = __dmul_rn(__dsqrt_rn(__dadd_rn(__dmul_rn(v.x, v.x), __dmul_rn(v.y, v.y))), NB_FRICTION);
@@ -228,24 +228,18 @@ __device__ __forceinline__ void integrate_body(const IntegrateArgs &a, int i, do
     if (xn < 0) {
         xn = 0;
         v.x = -v.x;
-    } else if (xn >= a.xdim) {
-        xn = a.xdim - 1;
+    } else if (xn >= xdim) {
+        xn = xdim - 1;
         v.x = -v.x;
     }
     if (yn < 0) {
         yn = 0;
         v.y = -v.y;
-    } else if (yn >= a.ydim) {
-        yn = a.ydim - 1;
+    } else if (yn >= ydim) {
+        yn = ydim - 1;
         v.y = -v.y;
     }
-    a.vel[i] = v;
-    const double2 pn = make_double2(xn, yn);
-    if (a.npeers > 0) {
-        for (int r = 0; r < a.npeers; ++r) a.peer_pos_new[r][i] = pn;   // every GPU's copy, over NVLink (incl. our own)
-    } else {
-        a.pos_new[i] = pn;
-    }
+    return make_double2(xn, yn);
 }
 
 // FAST: total force on body i from the partial sums, in a fixed order.  Directed kernel: the j-chunk
@@ -271,27 +265,80 @@ __device__ __forceinline__ void sum_partials(const IntegrateArgs &a, int i, doub
     }
 }
 
+// Block size: 128 threads, or TILE_J when the tile boxes of the new positions are fused in (a.boxes != nullptr,
+// a.lo % TILE_J == 0: CTA = one tile of the cell order; the force kernel's far-field test reads the boxes next
+// step, so the separate tile_boxes_kernel launch is only needed after a re-sort).
 template <int MODE>
-__global__ void __launch_bounds__(128) integrate_kernel(const IntegrateArgs a)
+__global__ void __launch_bounds__(TILE_J) integrate_kernel(const IntegrateArgs a)
 {
     __shared__ double s_tab[(MODE == MODE_EXACT) ? NBODY_DM_ATAN_TAB_LEN : 1];
+    __shared__ double s_red[(MODE == MODE_FAST) ? 5 : 1][TILE_J / 32];
     if (MODE == MODE_EXACT) {
         for (int k = threadIdx.x; k < NBODY_DM_ATAN_TAB_LEN; k += blockDim.x) s_tab[k] = c_atan_tab[k];
         __syncthreads();
     }
     const int i = a.lo + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= a.hi) return;
-    double xf, yf;
-    if (MODE == MODE_FAST) {
-        // fixed-order sum of the j-chunk partials: deterministic, independent of the GPU count
-        sum_partials(a, i, xf, yf);
-        a.frc[i] = make_double2(xf, yf);
-    } else {
-        const double2 t = a.frc[i];
-        xf = t.x;
-        yf = t.y;
+    const bool live = i < a.hi;
+    double2 pn = make_double2(0.0, 0.0);
+    double radius = 0.0;
+    if (live) {
+        double xf, yf;
+        if (MODE == MODE_FAST) {
+            // fixed-order sum of the j-chunk partials: deterministic, independent of the GPU count
+            sum_partials(a, i, xf, yf);
+            a.frc[i] = make_double2(xf, yf);
+        } else {
+            const double2 t = a.frc[i];
+            xf = t.x;
+            yf = t.y;
+        }
+        const double2 q = a.mr[i];
+        double2 v = a.vel[i];
+        pn = integrate_math<MODE>(a.pos_old[i], q, v, xf, yf, a.xdim, a.ydim, s_tab);
+        radius = q.y;
+        a.vel[i] = v;
+        if (a.npeers > 0) {
+            for (int r = 0; r < a.npeers; ++r) a.peer_pos_new[r][i] = pn;   // every GPU's copy, over NVLink (incl. our own)
+        } else {
+            a.pos_new[i] = pn;
+        }
     }
-    integrate_body<MODE>(a, i, xf, yf, s_tab);
+    if (MODE == MODE_FAST && a.boxes) {   // block-uniform
+        // boxes[tile] = {xmin, ymin, xmax, ymax, rmax, 0, 0, 0} of the tile's NEW positions (as tile_boxes_kernel)
+        double v[5] = {DBL_MAX, DBL_MAX, -DBL_MAX, -DBL_MAX, 0.0};
+        if (live) {
+            v[0] = pn.x; v[1] = pn.y; v[2] = pn.x; v[3] = pn.y;
+            v[4] = radius;
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            v[0] = fmin(v[0], __shfl_xor_sync(0xffffffffu, v[0], off));
+            v[1] = fmin(v[1], __shfl_xor_sync(0xffffffffu, v[1], off));
+            v[2] = fmax(v[2], __shfl_xor_sync(0xffffffffu, v[2], off));
+            v[3] = fmax(v[3], __shfl_xor_sync(0xffffffffu, v[3], off));
+            v[4] = fmax(v[4], __shfl_xor_sync(0xffffffffu, v[4], off));
+        }
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        if (lane == 0) {
+#pragma unroll
+            for (int q = 0; q < 5; ++q) s_red[q][warp] = v[q];
+        }
+        __syncthreads();
+        if (threadIdx.x < SYM_BOX_DOUBLES) {
+            const int q = threadIdx.x;
+            double r = 0.0;
+            if (q < 5) {
+                r = s_red[q][0];
+                for (int w = 1; w < TILE_J / 32; ++w) r = (q < 2) ? fmin(r, s_red[q][w]) : fmax(r, s_red[q][w]);
+            }
+            const size_t at = static_cast<size_t>((a.lo + blockIdx.x * TILE_J) / TILE_J) * SYM_BOX_DOUBLES + q;
+            if (a.npeers > 0) {
+                for (int p = 0; p < a.npeers; ++p) a.peer_boxes[p][at] = r;
+            } else {
+                a.boxes[at] = r;
+            }
+        }
+    }
 }
 
 // FAST: frc[i] = sum over j-chunks of part[s][i], s ascending (the same order integrate_kernel uses);

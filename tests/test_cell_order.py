@@ -71,16 +71,15 @@ def test_cell_order_far_field_is_used_and_agrees_with_creation_order(nb, oracle)
         np.testing.assert_allclose(fs[1][sl], yf[sl], rtol=1e-10, atol=1e-10 * np.abs(yf[sl]).max())
 
 
-def test_cell_order_results_do_not_depend_on_how_steps_are_split(nb, oracle, monkeypatch):
+def test_cell_order_results_do_not_depend_on_how_steps_are_split(nb, oracle):
     """Re-sorts happen on a schedule that counts steps, also across graph launches (2 steps each)."""
-    monkeypatch.setenv("NBODY_SORT_INTERVAL", "3")
     n = 17000
     b = oracle.init_bodies(n)
     b.xv *= 3.0e4    # make bodies really move between sorts (DELTA_T is 5e-6)
     b.yv *= 3.0e4
     runs = []
     for split in ((8,), (1,) * 8, (2, 5, 1), (3, 3, 2), (7, 1)):
-        g = make(nb, b, sort=1)
+        g = make(nb, b, sort=1, sort_interval=3)
         assert g.describe()["sort_interval"] == 3
         for k in split:
             g.step(k)
@@ -89,7 +88,7 @@ def test_cell_order_results_do_not_depend_on_how_steps_are_split(nb, oracle, mon
         g.close()
     for r in runs[1:]:
         assert bits_equal(runs[0], r)
-    g = make(nb, b, sort=1, use_graph=-1)
+    g = make(nb, b, sort=1, sort_interval=3, use_graph=-1)
     g.step(8)
     assert bits_equal(runs[0], g.fetch())
     ref = b.copy()
@@ -150,18 +149,17 @@ def test_cell_order_render_paints_lowest_original_index(nb, oracle):
     assert np.array_equal(gs.render(xdim, ydim), ref)
 
 
-def test_cell_order_same_bits_on_1_2_4_8_gpus(nb, oracle, monkeypatch):
+def test_cell_order_same_bits_on_1_2_4_8_gpus(nb, oracle):
     k = nb.device_count()
     if k < 2:
         pytest.skip("needs >= 2 GPUs")
-    monkeypatch.setenv("NBODY_SORT_INTERVAL", "2")
     n, steps = 20000, 5
     b = oracle.init_bodies(n)
     b.xv *= 3.0e4
     b.yv *= 3.0e4
     b.x[n - 1], b.y[n - 1] = b.x[1], b.y[1]
     def run(p, p2p=0):
-        g = make(nb, b, ngpus=p, sort=1, p2p=p2p)
+        g = make(nb, b, ngpus=p, sort=1, p2p=p2p, sort_interval=2)
         g.step(2)
         g.step(steps - 2)
         out = g.fetch()
