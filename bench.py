@@ -10,23 +10,37 @@ fast mode, STRONG scaling: the same 262144 bodies are sharded over the GPUs (row
 kernel); the per-step exchange that replaces MPI_Allgatherv (nbody-par.c:913) is fused into the kernels over
 NVLink peer memory (or one ncclAllGather when the GPUs cannot map each other).
 A step = one force + integrate (+ exchange) pass.  value = K * N * (N-1) / t, t = device time of
-the K-step loop (CUDA events on the library's stream), max over ranks.
+the K-step loop on the production path (nbody_gpu_step_bench: CUDA-graph launches, CUDA events on the library's
+stream, a 192 MiB L2 flush before every graph launch inside the span), max over ranks.
 
-e2e: the same metric through the C ABI with HOST buffers every step: nbody_gpu_set_state (H2D
-from the library's pinned staging) -> nbody_gpu_step(1) -> nbody_gpu_fetch (D2H), wall clock.
+e2e: the same metric through the C ABI with HOST buffers every step: nbody_gpu_set_state (H2D) ->
+nbody_gpu_step(1) -> nbody_gpu_fetch (D2H), wall clock; the caller's six arrays are page-locked once
+(nbody_gpu_pin_host), like a long-lived `struct world`.
 
 roofline: the force kernel is FP64-pipe bound (neither HBM nor tensor): achieved = algorithmic
 flops by the reference's own model (nbody-seq.c:367-380: 20 flop per unordered pair = 10 per
-directed pair-interaction) / the kernel's mean duration from per-launch CUDA events inside the
-timed region; peak = the DFMA rate measured live by nbody_gpu_fp64_peak (MEASURED_PEAKS.json has
+directed pair-interaction) / the kernel's mean duration from per-launch CUDA events (a second pass of K steps
+right after the timed one: nbody_gpu_step_profiled, plain launches with an event between the phases);
+peak = the DFMA rate measured live by nbody_gpu_fp64_peak (MEASURED_PEAKS.json has
 no FP64 figure).  pipe_frac = FP64-pipe instructions actually issued per pair (SASS count,
 confirmed by ncu sm__inst_executed_pipe_fp64) x pairs/s / (peak/2): the utilisation figure the
 north star's "% of FP64 pipe peak" means (an IEEE-grade rsqrt makes one unordered pair 19 pipe
 instructions = 9.5 per interaction, so the algorithmic-flop fraction cannot approach 1).
+traffic = DRAM bytes per force-kernel launch from the committed ncu captures (profiles/r2_traffic.json,
+written by tools/ncu_traffic.py from the .ncu-rep), keyed by kernel, N and GPU count.
 
---impl reference: the reference's CPU algorithm (oracle port, libm trig, row form = nbody-par's
-pass B, nbody-par.c:302-308) on all host cores, each step a bounded sample of rows of the same
-N = 262144 workload.  The oracle is only ever executed in that arm and in cpu_baseline.
+parity (N > 1): after the timed region every rank re-runs 3 steps from the initial state on the sharded handle and
+on a one-GPU handle on its own device; `bits_equal_to_1gpu` is true only if all six arrays agree bit for bit on
+every rank.
+
+configs (N = 1): the other BASELINE configs through the same C ABI: C1 32 x 100000 and 128 x 1000 (exact, the
+one-launch step loop; beside the reference's own nbody-seq timed on this host), C2 4096 x 1000 exact, C3 65536 x 200 fast.
+
+--impl reference: the reference's own parallel program (unmodified nbody-par.c built by oracle/Makefile against
+the fork/shared-memory MPI stand-in, one rank per host core) for ONE full step of the same N = 262144 workload
+(kind "reference"), cross-checked by the oracle port's rows sample; the port sample alone (kind "port") when the
+binary is missing or a full step would take more than ~7 minutes on this host.  The oracle is only ever
+executed in that arm and in cpu_baseline.
 """
 import argparse
 import json
@@ -65,6 +79,12 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the BASELINE config 1-3 block of the N = 1 line")
+    ap.add_argument("--no-parity", action="store_true", help="skip the bits-equal-to-one-GPU block of the N > 1 line")
+    ap.add_argument("--no-reference-full-step", action="store_true",
+                    help="--impl reference: port sample only (skip the reference binary's full step)")
+    ap.add_argument("--reference-full-step-limit", type=float, default=420.0,
+                    help="--impl reference: longest predicted full step (s) the reference binary is run for")
     return ap.parse_args()
 
 
@@ -155,11 +175,10 @@ def cpu_seq_sample(oracle_lib, b, n, budget_s):
     return 2.0 * ev / dt, rows2, dt
 
 
-def reference_binary_check(n_small=16384, steps=2):
+def run_reference_binary(n, steps, timeout=900):
     """The reference's OWN parallel program (unmodified nbody-par.c built by oracle/Makefile against the
-    fork/shared-memory MPI stand-in; MAXBODIES raised) on all host cores, pure MPI (one rank per core), at a
-    size it finishes in seconds.  Per-pair cost does not depend on N, so this pins the port's rate to the real
-    thing.  Returns None if oracle/_ref/nbody-par-big is not built."""
+    fork/shared-memory MPI stand-in; MAXBODIES raised) on all host cores, pure MPI (one rank per core).
+    Returns None if oracle/_ref/nbody-par-big is not built or the run fails."""
     exe = os.path.join(ROOT, "oracle", "_ref", "nbody-par-big")
     if not os.path.exists(exe):
         return None
@@ -171,8 +190,8 @@ def reference_binary_check(n_small=16384, steps=2):
         oracle_lib.write_ppm(ppm, XDIM, YDIM)
         env = dict(os.environ, MPISHIM_NP=str(cores), OMP_NUM_THREADS="1")
         try:
-            r = subprocess.run([exe, str(n_small), "0", ppm, str(steps)], env=env, cwd=d, stdout=subprocess.DEVNULL,
-                               stderr=subprocess.PIPE, text=True, timeout=300)
+            r = subprocess.run([exe, str(n), "0", ppm, str(steps)], env=env, cwd=d, stdout=subprocess.DEVNULL,
+                               stderr=subprocess.PIPE, text=True, timeout=timeout)
         except (OSError, subprocess.TimeoutExpired):
             return None
     took = [ln for ln in r.stderr.splitlines() if "N-body took" in ln]
@@ -180,8 +199,34 @@ def reference_binary_check(n_small=16384, steps=2):
         return None
     secs = float(took[0].split(":")[1].split()[0])
     return {"kind": "reference", "binary": "oracle/_ref/nbody-par-big (reference nbody-par.c + MPI stand-in)",
-            "ranks": cores, "threads_per_rank": 1, "n": n_small, "steps": steps, "seconds": secs,
-            "value": steps * n_small * (n_small - 1.0) / max(secs, 1e-9), "unit": UNIT}
+            "ranks": cores, "threads_per_rank": 1, "n": n, "steps": steps, "seconds": secs,
+            "value": steps * n * (n - 1.0) / max(secs, 1e-9), "unit": UNIT}
+
+
+def reference_binary_check(n_small=16384, steps=2):
+    """The reference binary at a size it finishes in seconds: per-pair cost does not depend on N, so this pins the
+    port's rate to the real thing (and predicts how long a full step of the headline N takes)."""
+    return run_reference_binary(n_small, steps, timeout=300)
+
+
+def reference_seq_seconds(n, steps):
+    """The reference's sequential program (oracle/_ref/nbody-seq, its Makefile's flags) on one host core: seconds of
+    its own "N-body took" line, or None if it is not built."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "nbody-seq")
+    if not os.path.exists(exe):
+        return None
+    import tempfile
+    import oracle_lib
+    with tempfile.TemporaryDirectory() as d:
+        ppm = os.path.join(d, "nbody.ppm")
+        oracle_lib.write_ppm(ppm, XDIM, YDIM)
+        try:
+            r = subprocess.run([exe, str(n), "0", ppm, str(steps)], cwd=d, stdout=subprocess.DEVNULL,
+                               stderr=subprocess.PIPE, text=True, timeout=120)
+        except (OSError, subprocess.TimeoutExpired):
+            return None
+    took = [ln for ln in r.stderr.splitlines() if "N-body took" in ln]
+    return float(took[0].split(":")[1].split()[0]) if (r.returncode == 0 and took) else None
 
 
 def run_reference(args, rank, world):
@@ -191,14 +236,14 @@ def run_reference(args, rank, world):
     import oracle_lib
     n = args.n
     threads = os.cpu_count() or 1
-    b = oracle_lib.init_bodies(n, XDIM, YDIM)
+    b = oracle_lib.init_bodies(n)
     L = oracle_lib.lib()
     xf, yf = np.zeros(n), np.zeros(n)
-    # size one "step" = a rows sample worth ~2 s so that steps+warmup stay within minutes
+    # port sample: one "step" = a rows sample worth ~1 s, so that steps+warmup stay well within a minute
     t0 = time.perf_counter()
     L.oracle_forces_rows(n, 0, 0, 4 * threads, threads, b.x, b.y, b.mass, b.radius, xf, yf)
     probe = time.perf_counter() - t0
-    rows = max(threads, int(2.0 / probe * 4 * threads) // threads * threads)
+    rows = max(threads, int(1.0 / probe * 4 * threads) // threads * threads)
     rows = min(rows, n)
     xn, yn = np.zeros(n), np.zeros(n)
 
@@ -213,25 +258,117 @@ def run_reference(args, rank, world):
     for _ in range(args.steps):
         one_step()
     dt = time.perf_counter() - t0
-    value = args.steps * rows * (n - 1.0) / dt
-    sample = "rows [0,%d) x all %d columns per step (%.3g of a full step), oracle row form, libm trig" % (
-        rows, n, rows / float(n))
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3 * (n / float(rows)),
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": {"workload": "N=%d bodies, reference initialiser, world %dx%d; "
-                                            "CPU sample of rows" % (n, XDIM, YDIM), "n": n},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
-            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0,
-            "note": "ms_per_step is the sample time scaled to a full step (x N/rows)"}
+    port_value = args.steps * rows * (n - 1.0) / dt
+    port = {"value": port_value, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": "rows [0,%d) x all %d columns per step (%.3g of a full step), oracle row form, libm trig, "
+                      "%d + %d such steps" % (rows, n, rows / float(n), args.warmup, args.steps)}
+
+    # the reference program itself: first at a size it finishes in seconds (predicts a full step), then ONE full step
     chk = reference_binary_check()
-    if chk:
-        line["cpu_baseline"]["reference_check"] = chk
+    full = None
+    if chk and not args.no_reference_full_step:
+        predicted = n * (n - 1.0) / chk["value"]
+        if predicted <= args.reference_full_step_limit:
+            full = run_reference_binary(n, 1, timeout=int(2.5 * predicted) + 120)
+    workload = "BASELINE config 4: N=%d bodies, reference initialiser (srand 27102015), world %dx%d" % (n, XDIM, YDIM)
+    if full:
+        value, ms_per_step = full["value"], full["seconds"] * 1e3
+        cpu = {"value": value, "unit": UNIT, "cores": threads, "kind": "reference",
+               "sample": "ONE full step of the same N=%d workload by the reference's own nbody-par.c (unmodified; MAXBODIES "
+                         "raised, int overflows of the init fixed; built against a fork/shared-memory MPI stand-in), %d ranks x 1 "
+                         "thread, its own 'N-body took' timer: %.1f s; --steps/--warmup apply to the port cross-check only"
+                         % (n, threads, full["seconds"]),
+               "port_cross_check": port, "reference_check_small": chk}
+        note = "one real full step of the reference program; ms_per_step is that step"
+    else:
+        value, ms_per_step = port_value, dt / args.steps * 1e3 * (n / float(rows))
+        cpu = dict(port)
+        if chk:
+            cpu["reference_check"] = chk
+        note = "port sample (the reference binary is missing or a full step would exceed the limit); ms_per_step is the sample time scaled to a full step (x N/rows)"
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": {"workload": workload + "; CPU: nbody-par MPI ranks on the host cores", "n": n,
+                                            "mode": "reference", "parallelism": "%d host cores" % threads},
+            "cpu_baseline": cpu,
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "note": note}
     print(json.dumps(line), flush=True)
 
 
 # ----------------------------------------------------------------------------------------------
+def state_sha256(arrays):
+    import hashlib
+    h = hashlib.sha256()
+    for a in arrays:
+        h.update(np.ascontiguousarray(a).tobytes())
+    return h.hexdigest()
+
+
+def load_traffic(kernel, n, gpus):
+    """DRAM bytes per force-kernel launch from the committed ncu captures (profiles/r2_traffic.json)."""
+    path = os.path.join(ROOT, "profiles", "r2_traffic.json")
+    try:
+        with open(path) as f:
+            table = json.load(f)
+    except (OSError, ValueError):
+        return None, None
+    for e in table.get("captures", []):
+        if e.get("kernel") == kernel and e.get("n") == n and e.get("gpus") == gpus:
+            return e.get("dram_bytes_read", 0.0) + e.get("dram_bytes_write", 0.0), \
+                "profiles/r2_traffic.json <- %s (dram__bytes_read.sum + dram__bytes_write.sum per launch)" % e.get("source")
+    return None, None
+
+
+def other_configs(nb, local_rank, peak_tf):
+    """BASELINE configs 1-3 through the same C ABI on one GPU (config 4 is the line itself, config 5 needs 8 GPUs)."""
+    out = {}
+
+    def run(n, mode, steps, reps=1):
+        x, y, xv, yv, mass, radius = nb.reference_init(n, XDIM, YDIM)
+        g = nb.NBodyGPU(x, y, xv, yv, mass, radius, xdim=XDIM, ydim=YDIM, mode=mode, device=local_rank)
+        g.step(2)
+        g.sync()
+        best = None
+        for _ in range(reps):
+            g.set_state(x, y, xv, yv)
+            g.sync()
+            t0 = time.perf_counter()
+            g.step(steps)
+            g.sync()
+            wall = time.perf_counter() - t0
+            best = wall if best is None else min(best, wall)
+        g.set_state(x, y, xv, yv)
+        ms = g.step_bench(steps, flush_l2=False)
+        d = g.describe()
+        far = g.far_fraction() if d.get("cell_order") else 0.0
+        g.close()
+        return best, ms * 1e-3, d, far
+
+    for n, steps in ((32, 100000), (128, 1000)):
+        wall, dev, d, _ = run(n, nb.MODE_EXACT, steps, reps=2)
+        cpu_s = reference_seq_seconds(n, steps)
+        out["c1_%dx%d_exact" % (n, steps)] = {
+            "seconds": wall, "device_seconds": dev, "steps_per_s": steps / wall, "kernel": d["kernel"],
+            "launches_for_the_run": 1 if d.get("single_launch_loop") else None,
+            "cpu_seconds_reference_nbody_seq_1core": cpu_s, "speedup_vs_nbody_seq": (cpu_s / wall) if cpu_s else None,
+            "checked_by": "tests/test_gpu_parity.py::test_exact_golden_* (byte-identical text, bit-identical state)"}
+    wall, dev, d, _ = run(4096, nb.MODE_EXACT, 1000)
+    out["c2_4096x1000_exact"] = {"seconds": wall, "ms_per_step": dev * 1e3 / 1000, "steps_per_s": 1000 / wall, "kernel": d["kernel"],
+                                 "pair_interactions_per_s": 1000 * 4096 * 4095.0 / dev,
+                                 "checked_by": "tests/test_gpu_parity.py::test_exact_4096_config2_prefix_and_graph_independence"}
+    wall, dev, d, far = run(65536, nb.MODE_FAST, 200)
+    rate = 200 * 65536 * 65535.0 / dev
+    ipp = 9.5 * (1.0 - far) + 8.5 * far
+    out["c3_65536x200_fast"] = {"seconds": wall, "ms_per_step": dev * 1e3 / 200, "steps_per_s": 200 / wall, "kernel": d["kernel"],
+                                "pair_interactions_per_s": rate, "far_field_fraction": far,
+                                "pipe_frac": ipp * rate / (peak_tf * 1e12 / 2.0),
+                                "ncu": "profiles/r2_ncu_forces_sym_N65536.txt",
+                                "checked_by": "tests/test_gpu_parity.py::test_baseline_configs_3_and_4_*"}
+    return out
+
+
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -262,9 +399,9 @@ def main():
     mode = nb.MODE_FAST if args.mode == "fast" else nb.MODE_EXACT
     # the reference's synthetic initial state (nbody-par.c:208-222) from the library's own host helper
     bx, by, bxv, byv, bmass, bradius = nb.reference_init(n, XDIM, YDIM)
+    p2p_cfg = int(os.environ.get("NBODY_BENCH_P2P", "0"))   # development: -1 = NCCL exchange
     g = nb.NBodyGPU(bx, by, bxv, byv, bmass, bradius, xdim=XDIM, ydim=YDIM, mode=mode,
-                    device=local_rank, rank=rank, nranks=world, nccl_id=nccl_id, jsplit=args.jsplit,
-                    p2p=int(os.environ.get("NBODY_BENCH_P2P", "0")))   # development: -1 = NCCL exchange
+                    device=local_rank, rank=rank, nranks=world, nccl_id=nccl_id, jsplit=args.jsplit, p2p=p2p_cfg)
 
     def barrier():
         if dist is not None:
@@ -280,11 +417,12 @@ def main():
 
     peak_tf, _ = nb.fp64_peak(local_rank, 200)
 
-    # ---- device-resident timed region ------------------------------------------------------
+    # ---- device-resident timed region: the production path (CUDA graphs) -------------------
     g.step(args.warmup)
-    g.step_profiled(1, flush_l2=True)   # one more untimed step on the timed path: its scratch buffer exists afterwards
+    g.step_bench(2, flush_l2=True)      # untimed: the flush scratch and the graphs exist afterwards
+    g.step_profiled(1, flush_l2=True)   # untimed: the event pool of the per-phase pass exists afterwards
     g.sync()
-    l0 = sum(g.launch_count()[1][:3])   # our kernels only (force, integrate, reduce), not NCCL's
+    l0 = sum(g.launch_count()[1][:3])   # our kernels only (force, integrate, others), not NCCL's
     # the sampler (a fork of nvidia-smi: tens of ms on an 8-GPU box) starts BEFORE the barrier, so that rank 0 does
     # not enter the timed region late and leave the other ranks waiting for it in their first exchange
     sampler = ClockSampler(local_rank)   # every rank records its own GPU
@@ -292,6 +430,10 @@ def main():
     time.sleep(0.3)
     barrier()
     t_region0 = time.perf_counter()
+    t_ms = g.step_bench(args.steps, flush_l2=True)
+    launches = sum(g.launch_count()[1][:3]) - l0
+    barrier()
+    # ---- the same K steps once more with an event between the phases (plain launches): kernel durations -----
     prof = g.step_profiled(args.steps, flush_l2=True)
     t_region1 = time.perf_counter()
     barrier()
@@ -309,8 +451,8 @@ def main():
         clocks["per_rank_samples"] = [int(r[2]) for r in per_rank]
         if any(r[3] > 0 for r in per_rank) and not clocks.get("reasons"):
             clocks["reasons"] = ["see other ranks"]
-    launches = sum(g.launch_count()[1][:3]) - l0
-    t_ms = maxreduce(prof["total"])
+    t_ms = maxreduce(t_ms)
+    prof_ms = maxreduce(prof["total"])
     force_ms = maxreduce(prof["force"])
     integ_ms = maxreduce(prof["integrate"])
     exch_ms = maxreduce(prof["exchange"])
@@ -321,8 +463,13 @@ def main():
     e2e = None
     if not args.no_e2e:
         host = g.fetch()                       # the caller's six arrays, reused every step like the reference's world struct
+        for a in host:
+            nb.pin_host(a)                     # allocated once, page-locked once (nbody_gpu_pin_host)
         x, y, xf, yf, xv, yv = host
         e_steps = max(2, min(args.steps, 5))
+        g.set_state(x, y, xv, yv)              # untimed round: first-touch of the pinned pages
+        g.step(1)
+        g.fetch(out=host)
         barrier()
         t0 = time.perf_counter()
         split = [0.0, 0.0, 0.0]
@@ -331,9 +478,8 @@ def main():
             g.set_state(x, y, xv, yv)          # H2D: positions + velocities
             tb = time.perf_counter()
             g.step(1)
-            g.sync()
             tc = time.perf_counter()
-            g.fetch(out=host)                  # D2H: the six columns the reference prints
+            g.fetch(out=host)                  # D2H: the six columns the reference prints (waits for the step)
             td = time.perf_counter()
             split[0] += tb - ta
             split[1] += tc - tb
@@ -342,10 +488,34 @@ def main():
         e_dt = maxreduce(time.perf_counter() - t0)
         e2e = {"value": e_steps * pairs_per_step / e_dt, "unit": UNIT,
                "h2d_bytes_per_step": 4 * 8 * n, "d2h_bytes_per_step": 6 * 8 * n, "steps": e_steps,
-               "call": "nbody_gpu_set_state + nbody_gpu_step(1) + nbody_gpu_fetch per step, wall clock",
-               "rank0_ms_per_step": {"set_state": 1e3 * split[0] / e_steps, "step": 1e3 * split[1] / e_steps,
-                                     "fetch": 1e3 * split[2] / e_steps}}
+               "ms_per_step": 1e3 * e_dt / e_steps,
+               "call": "nbody_gpu_set_state + nbody_gpu_step(1) + nbody_gpu_fetch per step, wall clock, host arrays "
+                       "page-locked once with nbody_gpu_pin_host",
+               "rank0_ms_per_step": {"set_state": 1e3 * split[0] / e_steps, "step_enqueue": 1e3 * split[1] / e_steps,
+                                     "fetch_incl_wait_for_step": 1e3 * split[2] / e_steps},
+               "h2d_bytes_per_step_per_rank": (4 * 8 * n) // world if "peer-memory" in g.describe().get("exchange", "") else 4 * 8 * n}
 
+    # ---- multi-rank parity: the sharded handle against one GPU, bit for bit, on every rank ---
+    parity = None
+    if world > 1 and not args.no_parity:
+        k = 3
+        g.set_state(bx, by, bxv, byv)
+        g.step(k)
+        sharded = g.fetch()
+        g1 = nb.NBodyGPU(bx, by, bxv, byv, bmass, bradius, xdim=XDIM, ydim=YDIM, mode=mode, device=local_rank, jsplit=args.jsplit)
+        g1.step(k)
+        single = g1.fetch()
+        g1.close()
+        same = all(np.array_equal(a.view(np.uint64), c.view(np.uint64)) for a, c in zip(sharded, single))
+        flag = torch.tensor([1 if same else 0], dtype=torch.int64, device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        parity = {"bits_equal_to_1gpu": bool(flag.item()), "steps": k, "ranks_checked": world,
+                  "sha256": state_sha256(sharded), "sha256_1gpu": state_sha256(single),
+                  "what": "set_state(initial) + step(%d) + fetch on the %d-rank handle vs a one-GPU handle on the same device, "
+                          "all six arrays, every rank (MIN-reduced)" % (k, world)}
+
+    desc = g.describe()
+    far = g.far_fraction() if desc.get("cell_order") else 0.0
     if rank != 0:
         g.close()
         if dist is not None:
@@ -357,27 +527,21 @@ def main():
     launch_pairs = rows * (n - 1.0)                       # pair-interactions one force launch evaluates
     launch_s = force_ms * 1e-3 / args.steps
     algo_tflops = 10.0 * launch_pairs / launch_s / 1e12   # reference flop model: 10 per directed pair
-    desc = g.describe()
     ipp = desc.get("fp64_instr_per_pair") or None
-    far = g.far_fraction() if desc.get("cell_order") else 0.0
     if ipp and far > 0.0:
         # far-field tiles issue 17 FP64-pipe instructions per unordered pair instead of 19 (forces_sym.cuh)
         ipp = ipp * (1.0 - far) + 8.5 * far
-    # DRAM bytes of one force-kernel launch from the committed ncu --set full capture of this very configuration
-    # (profiles/r1_ncu_forces_sym_wide_N262144.txt: read 24.6 MB + written 1.553 GB: the reaction and row partial sums);
-    # other configurations have no capture
-    traffic = None
-    if n == N_DEFAULT and world == 1 and desc.get("symmetric") and desc.get("cell_order"):
-        traffic = 24.6e6 + 1.5534e9   # bytes per launch (algorithmic: colpart N^2/1024*16 B = 1.07e9 + rowpart N*128*16 B = 0.54e9)
+    traffic, traffic_source = load_traffic(desc["kernel"], n, world)
     roofline = {"bound": "fp64", "achieved": algo_tflops, "peak": peak_tf, "unit": "TFLOP/s",
-                "frac": algo_tflops / peak_tf, "traffic": traffic,
-                "traffic_source": "profiles/r1_ncu_forces_sym_wide_N262144.txt (dram__bytes_read.sum + dram__bytes_write.sum, "
-                                  "bytes per launch)" if traffic else None,
-                "peak_source": "measured live: nbody_gpu_fp64_peak DFMA kernel on this GPU "
-                               "(MEASURED_PEAKS.json has no FP64 entry)",
+                "frac": algo_tflops / peak_tf, "traffic": traffic, "traffic_source": traffic_source,
+                "peak_source": "builder-measured live: nbody_gpu_fp64_peak DFMA kernel on this GPU "
+                               "(MEASURED_PEAKS.json has no FP64 entry; theory 148 SM x 64 lanes x 2 x 1.965 GHz = 37.2)",
                 "kernel": desc["kernel"], "evaluation": "symmetric (each unordered pair once)" if desc["symmetric"]
                 else "directed", "kernel_ms_per_launch": launch_s * 1e3,
-                "kernel_share_of_step": force_ms / t_ms,
+                "kernel_share_of_step": force_ms / prof_ms,
+                "timing": "mean of per-launch CUDA events over a second pass of the same K steps (plain launches, "
+                          "%.3f ms per step) right after the graph-launched timed pass (%.3f ms per step)"
+                          % (prof_ms / args.steps, t_ms / args.steps),
                 "algorithmic_flops_per_pair": 10, "pairs_per_launch": launch_pairs}
     if ipp:
         roofline["far_field_fraction"] = far
@@ -402,6 +566,11 @@ def main():
         if chk:
             cpu["reference_check"] = chk
 
+    configs = None
+    if world == 1 and not args.no_configs and n == N_DEFAULT:
+        configs = other_configs(nb, local_rank, peak_tf)
+
+    mb = lambda v: "%.0f MB" % (v / 1e6)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": t_ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -409,15 +578,22 @@ def main():
                                    "%s mode, row blocks sharded over %d GPU(s), per-step exchange: %s"
                                    % (n, XDIM, YDIM, args.mode, world, desc.get("exchange", "none")),
                        "n": n, "mode": args.mode, "parallelism": "row-shard x%d" % world,
-                       "l2": "256 MiB scratch overwritten between steps (L2 flush); working set per step 8 MiB"},
+                       "step_path": "CUDA graph of %d steps per launch" % desc["graph_steps"] if desc.get("graph_steps") else "plain launches",
+                       "l2": "192 MiB scratch overwritten before every graph launch, inside the timed span (L2 flush); "
+                             "besides, every step streams its partial sums through the L2 (%s written and re-read per "
+                             "force launch, the L2 holds 126 MB)" % (mb(traffic) if traffic else "see roofline.traffic")},
             "steps_per_s": args.steps / (t_ms * 1e-3),
             "phase_ms_per_step": {"force": force_ms / args.steps, "integrate": integ_ms / args.steps,
-                                  "exchange": exch_ms / args.steps},
+                                  "exchange": exch_ms / args.steps, "whole_step_plain_launches": prof_ms / args.steps},
             "clocks": clocks, "gpu_launches": launches, "roofline": roofline}
     if e2e:
         line["e2e"] = e2e
+    if parity:
+        line["parity"] = parity
     if cpu:
         line["cpu_baseline"] = cpu
+    if configs:
+        line["configs"] = configs
     print(json.dumps(line), flush=True)
     g.close()
     if dist is not None:

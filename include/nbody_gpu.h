@@ -103,6 +103,11 @@ int nbody_gpu_step(nbody_gpu *h, int steps);
  * synchronised; *ms receives the device time (max over this handle's devices). */
 int nbody_gpu_step_timed(nbody_gpu *h, int steps, float *ms);
 
+/* As nbody_gpu_step_timed -- the production path: CUDA-graph launches, or the one-launch loop of a small world --
+ * with, if flush_l2 != 0, a 192 MiB scratch buffer (larger than the L2) overwritten before every launch unit,
+ * inside the timed span.  What bench.py reports as `value`. */
+int nbody_gpu_step_bench(nbody_gpu *h, int steps, int flush_l2, float *ms);
+
 /* As nbody_gpu_step_timed with plain launches (no CUDA graph, no single-launch loop) and a CUDA event
  * between the phases of every step: out_ms[0] = whole span, [1] = sum of force-kernel spans, [2] = integrate kernels,
  * [3] = position exchange (0 when not sharded); each the max over this handle's devices.
@@ -160,6 +165,14 @@ int nbody_gpu_describe(const nbody_gpu *h, char *buf, int len);
  * (the last ones may be short or empty) so that one ncclAllGather replaces
  * MPI_Allgatherv (nbody-par.c:913-917). */
 void nbody_gpu_partition(int n, int nranks, int rank, int *lo, int *hi);
+
+/* How a job of `nranks` GPUs would share n bodies (host arithmetic only, no device needed; the library's own
+ * sharding code, for tests and capacity planning): out[0..1] = rows [lo, hi) this rank integrates;
+ * out[7] = 1 if the symmetric kernel is used (fast mode, n >= 8192, nranks divides 8) and then out[2..3] = first
+ * and number of the 8 virtual ranks owned, out[4] = row blocks (512 rows) whose pairs this rank evaluates,
+ * out[5] = j-chunks, out[6] = long chunks among them; *pair_evaluations = pair formulas this rank evaluates per
+ * step (symmetric: each unordered pair once, directed inside a row block; else rows x n). */
+int nbody_gpu_shard_plan(int n, int mode, int nranks, int rank, int out[8], long long *pair_evaluations);
 
 /* The reference's own partition rule, for comparison (nbody-par.c:225-263):
  * counts n/P, ranks 1..n%P get one more; displacements are the prefix sum. */

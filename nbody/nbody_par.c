@@ -19,6 +19,7 @@
  * --display-final (paint the final state into the PPM).  secs_per_update > 0 restores the timed
  * display() of nbody-seq (nbody-seq.c:467-471; dead code in nbody-par), rendered by a CUDA kernel.
  */
+#include <dirent.h>
 #include <errno.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -81,7 +82,10 @@ static void write_image(nbody_gpu *h, const char *path, long data_offset, int xd
     size_t bytes = (size_t)xdim * ydim * 3;
     unsigned char *img = malloc(bytes);
     FILE *f;
-    if (!img) return;
+    if (!img) {
+        fprintf(stderr, "Cannot malloc(%zu) for the image of %s\n", bytes, path);
+        exit(1);
+    }
     if (nbody_gpu_render(h, img) != 0) {
         fprintf(stderr, "nbody_gpu_render: %s\n", nbody_gpu_last_error());
         exit(1);
@@ -95,6 +99,42 @@ static void write_image(nbody_gpu *h, const char *path, long data_offset, int xd
     }
     free(img);
 }
+
+#ifndef NBODY_SEQ
+/* --run-xps: the reference reads NODES and CPUS_PER_NODE back from the <job>.PRUN_ENVIRONMENT file the cluster
+ * launcher leaves in the working directory (nbody-par.c:441-517: PRUN_CPUS / PRUN_CPUS_PER_NODE and
+ * PRUN_CPUS_PER_NODE).  Same here (bin/prun writes that file); without one: 1 node, `fallback_cpus` per node. */
+static void prun_compute_args(int *nodes, int *cpus_per_node, int fallback_cpus)
+{
+    DIR *dr = opendir(".");
+    struct dirent *en;
+    char name[512] = "";
+    *nodes = 1;
+    *cpus_per_node = fallback_cpus;
+    if (!dr) return;
+    while ((en = readdir(dr)) != NULL) {
+        if (strstr(en->d_name, ".PRUN_ENVIRONMENT") != NULL) {
+            snprintf(name, sizeof name, "%s", en->d_name);
+            break;
+        }
+    }
+    closedir(dr);
+    if (!name[0]) return;
+    FILE *f = fopen(name, "r");
+    if (!f) return;
+    char line[1000];
+    int cpus = 0, per_node = 0;
+    while (fgets(line, sizeof line, f) != NULL) {
+        if (strncmp(line, "PRUN_CPUS=", 10) == 0) cpus = atoi(line + 10);
+        else if (strncmp(line, "PRUN_CPUS_PER_NODE=", 19) == 0) per_node = atoi(line + 19);
+    }
+    fclose(f);
+    if (cpus > 0 && per_node > 0) {
+        *nodes = cpus / per_node;   /* prun multiplies -np by -<cpus>: dividing gives back the -np argument */
+        *cpus_per_node = per_node;
+    }
+}
+#endif
 
 static long long nr_flops(long long n, long long steps)
 {
@@ -197,12 +237,17 @@ int main(int argc, char **argv)
     cfg.n = n; cfg.xdim = xdim; cfg.ydim = ydim; cfg.mode = mode;
     cfg.ngpus = ngpus; cfg.device = ngpus > 1 ? -1 : 0;
     nbody_gpu *h = NULL;
+    /* the world is allocated once and lives for the whole run (nbody-par.c:810): page-lock it so that the upload
+     * and the final fetch run at PCIe speed; the run works without (pageable copies are staged by the driver) */
+    const int pinned = nbody_gpu_pin_host(buf, (size_t)n * 8 * sizeof(double)) == 0;
     if (nbody_gpu_init(&h, &cfg, x, y, xv, yv, mass, radius) != 0) die_gpu("nbody_gpu_init");
 
     double comm_overhead = 0;
     (void)comm_overhead;
     const double start = now_seconds();
     if (measure_comm && run_xps) {
+        /* nbody-par.c:912,918: time spent in the exchange, here from device timers between the phases of every
+         * step; that needs plain launches (no CUDA graph), so RTIME of such a run includes the launch gaps */
         float ms[4];
         if (nbody_gpu_step_profiled(h, steps, 0, ms) != 0) die_gpu("nbody_gpu_step_profiled");
         comm_overhead = ms[3] / 1000.0;
@@ -236,8 +281,11 @@ int main(int argc, char **argv)
 #ifdef NBODY_SEQ
         printf("%d,%.3f, %.2f\n", n, rtime, gflops);
 #else
-        /* SIZE,NODES,CPUS_PER_NODE,NBODIES,RTIME,COMMTIME,COMMTIME:RTIME,GFLOPS -- one node, ngpus GPUs */
-        printf("%d,%d,%d,%d,%.3f,%.3f,%.3f,%.2f\n", ngpus, 1, ngpus, n, rtime, comm_overhead,
+        /* SIZE,NODES,CPUS_PER_NODE,NBODIES,RTIME,COMMTIME,COMMTIME:RTIME,GFLOPS (nbody-par.c:954-957): SIZE = the
+         * GPUs that shared the rows (the reference: MPI ranks), NODES/CPUS_PER_NODE as the launcher recorded them */
+        int nodes = 1, cpus_per_node = ngpus;
+        prun_compute_args(&nodes, &cpus_per_node, ngpus);
+        printf("%d,%d,%d,%d,%.3f,%.3f,%.3f,%.2f\n", ngpus, nodes, cpus_per_node, n, rtime, comm_overhead,
                comm_overhead / rtime, gflops);
 #endif
     }
@@ -248,6 +296,7 @@ int main(int argc, char **argv)
             rtime > 0 ? (double)steps * n * (n - 1.0) / rtime : 0.0, rtime > 0 ? steps / rtime : 0.0);
 
     nbody_gpu_destroy(h);
+    if (pinned) nbody_gpu_unpin_host(buf);
     free(buf);
     return 0;
 }

@@ -172,6 +172,35 @@ void oracle_forces_rows(int n, int trig, int lo, int hi, int threads,
     }
 }
 
+/* oracle_forces_rows for a LIST of bodies (any order): the sums of rows[0..nrows) only, each exactly as above.
+ * For sampled checks at sizes where all rows would take hours on the CPU. */
+void oracle_forces_row_list(int n, int trig, int nrows, const int *rows, int threads,
+                            const double *x, const double *y,
+                            const double *mass, const double *radius,
+                            double *xf, double *yf)
+{
+    if (threads < 1) threads = 1;
+#pragma omp parallel for schedule(dynamic, 1) num_threads(threads)
+    for (int k = 0; k < nrows; ++k) {
+        const int i = rows[k];
+        double ax = 0, ay = 0;
+        for (int j = 0; j < i; ++j) {
+            double fx, fy;
+            pair_force(trig, x[j], y[j], mass[j], radius[j], x[i], y[i], mass[i], radius[i], &fx, &fy);
+            ax -= fx;
+            ay -= fy;
+        }
+        for (int j = i + 1; j < n; ++j) {
+            double fx, fy;
+            pair_force(trig, x[i], y[i], mass[i], radius[i], x[j], y[j], mass[j], radius[j], &fx, &fy);
+            ax += fx;
+            ay += fy;
+        }
+        xf[i] = ax;
+        yf[i] = ay;
+    }
+}
+
 /* compute_velocities: nbody-seq.c:114-130.  XF/YF are read, not modified. */
 void oracle_velocities(int n, int trig, const double *xf, const double *yf,
                        const double *mass, double *xv, double *yv)

@@ -60,6 +60,7 @@ def lib():
     L.nbody_gpu_set_state.argtypes = [vp] + [_dp] * 4
     L.nbody_gpu_step.argtypes = [vp, ci]
     L.nbody_gpu_step_timed.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_float)]
+    L.nbody_gpu_step_bench.argtypes = [vp, ci, ci, ctypes.POINTER(ctypes.c_float)]
     L.nbody_gpu_step_profiled.argtypes = [vp, ci, ci, ctypes.POINTER(ctypes.c_float)]
     L.nbody_gpu_forces.argtypes = [vp, _dp, _dp]
     L.nbody_gpu_fetch.argtypes = [vp] + [odp] * 6
@@ -84,6 +85,7 @@ def lib():
     L.nbody_gpu_device_count.restype = ci
     L.nbody_gpu_fp64_peak.argtypes = [ci, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
     L.nbody_gpu_abi_version.restype = ci
+    L.nbody_gpu_shard_plan.argtypes = [ci, ci, ci, ci, ctypes.POINTER(ci), ctypes.POINTER(ctypes.c_longlong)]
     L.nbody_gpu_pin_host.argtypes = [vp, ctypes.c_size_t]
     L.nbody_gpu_unpin_host.argtypes = [vp]
     _lib = L
@@ -116,6 +118,15 @@ def partition_reference(n, nranks):
     displs = (ctypes.c_int * nranks)()
     lib().nbody_gpu_partition_reference(n, nranks, counts, displs)
     return list(counts), list(displs)
+
+
+def shard_plan(n, mode, nranks, rank):
+    """How rank `rank` of `nranks` GPUs shares n bodies (host arithmetic of the library's sharding)."""
+    out = (ctypes.c_int * 8)()
+    ev = ctypes.c_longlong()
+    _check(lib().nbody_gpu_shard_plan(n, mode, nranks, rank, out, ctypes.byref(ev)))
+    return dict(lo=out[0], hi=out[1], v0=out[2], nv=out[3], row_blocks=out[4], chunks=out[5], long_chunks=out[6],
+                symmetric=bool(out[7]), pair_evaluations=ev.value)
 
 
 def reference_init(n, xdim=1024, ydim=768):
@@ -177,6 +188,13 @@ class NBodyGPU:
         """Run `steps` steps bracketed by CUDA events on the library's stream; returns milliseconds."""
         ms = ctypes.c_float()
         _check(lib().nbody_gpu_step_timed(self._h, int(steps), ctypes.byref(ms)))
+        return ms.value
+
+    def step_bench(self, steps=1, flush_l2=True):
+        """The production step path (CUDA graphs / one-launch loop) between two CUDA events, with an L2 flush before
+        every launch unit; returns milliseconds."""
+        ms = ctypes.c_float()
+        _check(lib().nbody_gpu_step_bench(self._h, int(steps), int(bool(flush_l2)), ctypes.byref(ms)))
         return ms.value
 
     def step_profiled(self, steps=1, flush_l2=False):

@@ -36,13 +36,46 @@ int launch_forces_exact(const ForceArgs &a, cudaStream_t st)
     return 0;
 }
 
+// Cluster size of the one-launch step loop: 1 CTA up to SMALL_N_ONE_CTA bodies (no cluster barrier at all), else the
+// largest of 16 / 8 CTAs the device can co-schedule with this much shared memory (16 needs the non-portable
+// opt-in and a GPC with 16 free SMs).  The result does not depend on it: every body's fold order is fixed.
+static int small_cluster_for(int n, int device)
+{
+    if (n <= SMALL_N_ONE_CTA) return 1;
+    static int best[64] = {};
+    int &b = best[device & 63];
+    if (b) return b;
+    b = SMALL_CLUSTER;
+    if (cudaFuncSetAttribute(small_world_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess &&
+        cudaFuncSetAttribute(small_world_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             static_cast<int>(small_smem_bytes(SMALL_N_MAX, 16))) == cudaSuccess) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(16);
+        cfg.blockDim = dim3(SMALL_THREADS);
+        cfg.dynamicSmemBytes = small_smem_bytes(SMALL_N_MAX, 16);
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 16;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        int nclusters = 0;
+        if (cudaOccupancyMaxActiveClusters(&nclusters, small_world_kernel, &cfg) == cudaSuccess && nclusters >= 1) b = 16;
+    }
+    cudaGetLastError();
+    return b;
+}
+
 int launch_small_world(const SmallArgs &a, cudaStream_t st)
 {
     if (a.n < 1 || a.n > SMALL_N_MAX) return static_cast<int>(cudaErrorInvalidValue);
-    const size_t smem = small_smem_bytes(a.n);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const unsigned c = static_cast<unsigned>(small_cluster_for(a.n, dev));
+    const size_t smem = small_smem_bytes(a.n, static_cast<int>(c));
     cudaError_t e = cudaFuncSetAttribute(small_world_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) return static_cast<int>(e);
-    const unsigned c = static_cast<unsigned>(small_cluster_size(a.n));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(c);
     cfg.blockDim = dim3(SMALL_THREADS);

@@ -948,6 +948,48 @@ unsigned nbody_gpu_cell_key(double x, double y, int xdim, int ydim)
     return cell_key_host(x, y, 65535.0 / static_cast<double>(xdim > ydim ? xdim : ydim));
 }
 
+int nbody_gpu_shard_plan(int n, int mode, int nranks, int rank, int out[8], long long *pair_evaluations)
+{
+    if (n < 1 || nranks < 1 || rank < 0 || rank >= nranks || !out) return fail(NBODY_GPU_EINVAL, "bad argument");
+    int lo = 0, hi = 0;
+    partition(n, nranks, rank, &lo, &hi);
+    const bool fast = mode == NBODY_GPU_MODE_FAST;
+    const bool symmetric = fast && (SYM_V % nranks == 0) && n >= 8192;
+    for (int k = 0; k < 8; ++k) out[k] = 0;
+    out[0] = lo;
+    out[1] = hi;
+    long long evals = 0;
+    if (symmetric) {
+        const ChunkMap cm = choose_split_sym(n, 0);
+        const int nv = SYM_V / nranks, v0 = rank * nv;
+        const int nblocks = (n + SYM_RB - 1) / SYM_RB;
+        const int slots = (nblocks + 2 * SYM_V - 1) / (2 * SYM_V) * 2 * nv;
+        int owned = 0;
+        for (int k = 0; k < slots; ++k) {
+            const int B = sym_owned_block(k, v0, nv);
+            if (B >= nblocks) continue;
+            owned += 1;
+            // the kernel's walk: directed pairs inside the block's own tiles, one evaluation per pair above it
+            const long long rows = (B + 1) * SYM_RB <= n ? SYM_RB : n - B * SYM_RB;
+            evals += rows * rows + rows * static_cast<long long>(n - B * SYM_RB - rows);
+        }
+        out[2] = v0;
+        out[3] = nv;
+        out[4] = owned;
+        out[5] = cm.nsplit;
+        out[6] = cm.nbig;
+        out[7] = 1;
+    } else {
+        evals = static_cast<long long>(hi - lo) * n;   // directed: every owned row against all n columns
+        int nsplit = 1, chunk = n;
+        if (fast) choose_split(n, 0, &nsplit, &chunk);
+        out[5] = nsplit;
+        out[6] = nsplit;
+    }
+    if (pair_evaluations) *pair_evaluations = evals;
+    return NBODY_GPU_OK;
+}
+
 int nbody_gpu_nccl_unique_id(void *out)
 {
     if (!out) return fail(NBODY_GPU_EINVAL, "out is NULL");
@@ -1223,6 +1265,56 @@ int nbody_gpu_step_timed(nbody_gpu *h, int steps, float *ms)
         if (t > worst) worst = t;
     }
     rc = sync_all(h);   // also reads the peer-exchange error word
+    if (rc) return poison(h, rc);
+    *ms = worst;
+    return NBODY_GPU_OK;
+}
+
+int nbody_gpu_step_bench(nbody_gpu *h, int steps, int flush_l2, float *ms)
+{
+    int rc = check_usable(h);
+    if (rc) return rc;
+    if (!ms || steps < 0) return fail(NBODY_GPU_EINVAL, "bad argument");
+    const size_t flush_bytes = 192u << 20;   // larger than the 126 MB L2
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        if (flush_l2 && !s.flush) NB_CUDA(cudaMalloc(&s.flush, 256u << 20));   // first call only
+    }
+    rc = sync_all(h);
+    if (rc) return poison(h, rc);
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        NB_CUDA(cudaEventRecord(s.ev0, s.stream));
+    }
+    // the production path (graph launches / the one-launch loop), one launch unit at a time with the flush between
+    const int unit = h->small ? (steps > 0 ? steps : 1) : ((h->graph_steps > 0 && (!h->sharded || h->p2p)) ? h->graph_steps : 1);
+    int tick = 0;
+    for (int left = steps; left > 0;) {
+        const int k = left < unit ? left : unit;
+        if (flush_l2) {
+            for (Shard &s : h->shards) {
+                NB_CUDA(cudaSetDevice(s.device));
+                NB_CUDA(cudaMemsetAsync(s.flush, tick & 0xff, flush_bytes, s.stream));
+            }
+            ++tick;
+        }
+        rc = do_steps(h, k);
+        if (rc) return poison(h, rc);
+        left -= k;
+    }
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        NB_CUDA(cudaEventRecord(s.ev1, s.stream));
+    }
+    float worst = 0.f;
+    for (Shard &s : h->shards) {
+        NB_CUDA(cudaSetDevice(s.device));
+        NB_CUDA(cudaEventSynchronize(s.ev1));
+        float t = 0.f;
+        NB_CUDA(cudaEventElapsedTime(&t, s.ev0, s.ev1));
+        if (t > worst) worst = t;
+    }
+    rc = sync_all(h);
     if (rc) return poison(h, rc);
     *ms = worst;
     return NBODY_GPU_OK;

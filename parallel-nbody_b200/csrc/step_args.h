@@ -184,7 +184,7 @@ void launch_publish(const PublishArgs &a, cudaStream_t st);
 
 // The whole step loop of a small world in ONE launch (smalln.cuh, EXACT mode).
 constexpr int SMALL_N_MAX = 256;    // bodies
-constexpr int SMALL_N_ONE_CTA = 32; // up to here one CTA; above, a cluster of SMALL_CLUSTER CTAs
+constexpr int SMALL_N_ONE_CTA = 32; // up to here one CTA; above, a cluster of 16 CTAs (SMALL_CLUSTER where 16 cannot be co-scheduled)
 constexpr int SMALL_CLUSTER = 8;
 struct SmallArgs {
     double2 *pos[2];      // ping-pong positions in HBM; `cur` holds the state at entry

@@ -192,22 +192,33 @@ __global__ void __launch_bounds__(FORCE_THREADS) forces_kernel(const ForceArgs a
 // ---------------------------------------------------------------------------------
 // integrate_kernel: one thread per owned body.
 // ---------------------------------------------------------------------------------
-// compute_velocities + compute_positions for one body (nbody-seq.c:114-165): p = position, q = (mass, radius),
-// v = velocity (updated in place), (xf, yf) = the body's pair-force sum; returns the new position.
-template <int MODE>
-__device__ __forceinline__ double2 integrate_math(double2 p, double2 q, double2 &v, double xf, double yf, int xdim,
-                                                  int ydim, const double *tab)
+// The friction term of compute_velocities (nbody-seq.c:120-125): (force*cos(angle), force*sin(angle)) with
+// force = sqrt(xv^2+yv^2)*FRICTION, angle = atan2(yv, xv).  It depends on the velocity alone, not on the
+// pair forces, so the one-launch step loop (smalln.cuh) evaluates it beside the pair terms.
+__device__ __forceinline__ double2 friction_exact(double2 v, const double *tab)
 {
+    double force = __dmul_rn(__dsqrt_rn(__dadd_rn(__dmul_rn(v.x, v.x), __dmul_rn(v.y, v.y))), NB_FRICTION);
+    double angle = nbody_dm_atan2(v.y, v.x, tab);
+    double s, c;
+    nbody_dm_sincos(angle, &s, &c);
+    return make_double2(__dmul_rn(force, c), __dmul_rn(force, s));
+}
+
+// The rest of compute_velocities and compute_positions (nbody-seq.c:126-128,141-163): fric = the friction term
+// (EXACT) or unused (FAST: FRICTION*v, formed here); v is updated in place; returns the new position.
+template <int MODE>
+__device__ __forceinline__ double2 advance_body(double2 p, double2 q, double2 &v, double xf, double yf, double2 fric,
+                                                int xdim, int ydim)
+{
+    double xn, yn;
     if (MODE == MODE_EXACT) {
-        // compute_velocities, nbody-seq.c:120-128
-        double force = __dmul_rn(__dsqrt_rn(__dadd_rn(__dmul_rn(v.x, v.x), __dmul_rn(v.y, v.y))), NB_FRICTION);
-        double angle = nbody_dm_atan2(v.y, v.x, tab);
-        double s, c;
-        nbody_dm_sincos(angle, &s, &c);
-        double fx = __dsub_rn(xf, __dmul_rn(force, c));
-        double fy = __dsub_rn(yf, __dmul_rn(force, s));
+        double fx = __dsub_rn(xf, fric.x);
+        double fy = __dsub_rn(yf, fric.y);
         v.x = __dadd_rn(v.x, __dmul_rn(__ddiv_rn(fx, q.x), NB_DELTA_T));
         v.y = __dadd_rn(v.y, __dmul_rn(__ddiv_rn(fy, q.x), NB_DELTA_T));
+        // compute_positions uses the updated velocity
+        xn = __dadd_rn(p.x, __dmul_rn(v.x, NB_DELTA_T));
+        yn = __dadd_rn(p.y, __dmul_rn(v.y, NB_DELTA_T));
     } else {
         // friction acts along -v: sqrt(|v|^2)*FRICTION*(cos,sin)(atan2(yv,xv)) = FRICTION*(xv,yv)
         double fx = xf - NB_FRICTION * v.x;
@@ -215,13 +226,6 @@ __device__ __forceinline__ double2 integrate_math(double2 p, double2 q, double2 
         double im = NB_DELTA_T / q.x;
         v.x = fma(fx, im, v.x);
         v.y = fma(fy, im, v.y);
-    }
-    // compute_positions, nbody-seq.c:141-163 (uses the updated velocity)
-    double xn, yn;
-    if (MODE == MODE_EXACT) {
-        xn = __dadd_rn(p.x, __dmul_rn(v.x, NB_DELTA_T));
-        yn = __dadd_rn(p.y, __dmul_rn(v.y, NB_DELTA_T));
-    } else {
         xn = fma(v.x, NB_DELTA_T, p.x);
         yn = fma(v.y, NB_DELTA_T, p.y);
     }
@@ -240,6 +244,17 @@ __device__ __forceinline__ double2 integrate_math(double2 p, double2 q, double2 
         v.y = -v.y;
     }
     return make_double2(xn, yn);
+}
+
+// compute_velocities + compute_positions for one body (nbody-seq.c:114-165): p = position, q = (mass, radius),
+// v = velocity (updated in place), (xf, yf) = the body's pair-force sum; returns the new position.
+template <int MODE>
+__device__ __forceinline__ double2 integrate_math(double2 p, double2 q, double2 &v, double xf, double yf, int xdim,
+                                                  int ydim, const double *tab)
+{
+    double2 fric = make_double2(0.0, 0.0);
+    if (MODE == MODE_EXACT) fric = friction_exact(v, tab);
+    return advance_body<MODE>(p, q, v, xf, yf, fric, xdim, ydim);
 }
 
 // FAST: total force on body i from the partial sums, in a fixed order.  Directed kernel: the j-chunk

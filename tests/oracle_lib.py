@@ -31,6 +31,7 @@ def lib():
     L.oracle_init_bodies.argtypes = [i, i, i] + [_dp] * 6
     L.oracle_forces_symmetric.argtypes = [i, i] + [_dp] * 6
     L.oracle_forces_rows.argtypes = [i, i, i, i, i] + [_dp] * 6
+    L.oracle_forces_row_list.argtypes = [i, i, i, np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS"), i] + [_dp] * 6
     L.oracle_forces_symmetric_sample.argtypes = [i, i, i, i] + [_dp] * 6
     L.oracle_forces_symmetric_sample.restype = ctypes.c_longlong
     L.oracle_velocities.argtypes = [i, i] + [_dp] * 5
@@ -76,6 +77,49 @@ def run(b, steps, trig, xdim=1024, ydim=768, threads=1):
                           b.x, b.y, b.xf, b.yf, b.xv, b.yv, b.mass, b.radius)
     assert rc == 0
     return b
+
+
+def forces_for(rows, x, y, mass, radius, trig=0, threads=0):
+    """Pair-force sums of the listed bodies only (oracle row form): (xf[rows], yf[rows])."""
+    n = len(x)
+    rows = np.ascontiguousarray(rows, dtype=np.int32)
+    xf, yf = np.zeros(n), np.zeros(n)
+    lib().oracle_forces_row_list(n, trig, len(rows), rows, threads or (os.cpu_count() or 1),
+                                 np.ascontiguousarray(x), np.ascontiguousarray(y), mass, radius, xf, yf)
+    return xf[rows], yf[rows]
+
+
+def step_bodies(rows, x, y, xv, yv, xf_rows, yf_rows, mass, trig=0, xdim=1024, ydim=768):
+    """compute_velocities + compute_positions (oracle) for the listed bodies, given their force sums:
+    returns (x', y', xv', yv') of those bodies."""
+    rows = np.asarray(rows)
+    m = len(rows)
+    sxv, syv = np.ascontiguousarray(xv[rows]), np.ascontiguousarray(yv[rows])
+    lib().oracle_velocities(m, trig, np.ascontiguousarray(xf_rows), np.ascontiguousarray(yf_rows),
+                            np.ascontiguousarray(mass[rows]), sxv, syv)
+    xn, yn = np.zeros(m), np.zeros(m)
+    lib().oracle_positions(m, xdim, ydim, np.ascontiguousarray(x[rows]), np.ascontiguousarray(y[rows]), sxv, syv, xn, yn)
+    return xn, yn, sxv, syv
+
+
+def cell_order(nb, x, y, xdim=1024, ydim=768):
+    """Slot order of the library's cell order for these positions: bodies sorted by (Hilbert cell key, index),
+    from the library's host mirror of the key.  order[s] = body in slot s."""
+    keys = np.fromiter((nb.cell_key(float(a), float(b), xdim, ydim) for a, b in zip(x, y)), dtype=np.int64, count=len(x))
+    return np.lexsort((np.arange(len(x)), keys))
+
+
+def block_sample(order, rb=512, per_block_extra=1, seed=1):
+    """Bodies that sit at row-block boundaries of the symmetric kernel (first and last slot of every block of
+    `rb` slots) plus `per_block_extra` random slots per block."""
+    n = len(order)
+    rng = np.random.default_rng(seed)
+    slots = []
+    for b0 in range(0, n, rb):
+        b1 = min(n, b0 + rb)
+        slots += [b0, b1 - 1]
+        slots += list(rng.integers(b0, b1, per_block_extra))
+    return np.unique(order[np.array(slots)])
 
 
 def display(b, xdim=1024, ydim=768):

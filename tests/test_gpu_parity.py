@@ -291,12 +291,47 @@ def test_baseline_configs_3_and_4_full_size_properties(nb, oracle, n, steps):
         assert np.array_equal(a.view(np.uint64), c.view(np.uint64))
     assert s[0].min() >= 0 and s[0].max() < 1024 and s[1].min() >= 0 and s[1].max() < 768
     assert abs(s[2].sum()) <= 1e-9 * np.abs(s[2]).sum() and abs(s[3].sum()) <= 1e-9 * np.abs(s[3]).sum()
-    # forces at the final positions (the state after the last step), sampled rows vs the CPU oracle
+    # forces at the final positions (the state after the last step) against the CPU oracle, for the bodies that sit
+    # at the edges of EVERY row block of the symmetric kernel (first and last slot of each 512-slot block of the
+    # cell order: block-boundary rows, last lane of a rotation group, tiles next to the diagonal, the partial last
+    # tile) plus one random slot per block: 3 x N/512 rows x N columns on the CPU
+    order = oracle.cell_order(nb, b.x, b.y)          # the order of the only sort of this run (steps < 256)
+    rows = oracle.block_sample(order)
+    assert len(rows) >= 2 * (n // 512)
     fx, fy = gs.forces()
-    xf, yf = np.zeros(n), np.zeros(n)
-    rows = 8
-    for lo in (0, n // 2 + 3, n - rows):
-        oracle.lib().oracle_forces_rows(n, 0, lo, lo + rows, 8, s[0], s[1], b.mass, b.radius, xf, yf)
-        sl = slice(lo, lo + rows)
-        sc = max(np.abs(xf[sl]).max(), np.abs(yf[sl]).max())
-        assert np.abs(fx[sl] - xf[sl]).max() <= 1e-10 * sc and np.abs(fy[sl] - yf[sl]).max() <= 1e-10 * sc
+    xf, yf = oracle.forces_for(rows, s[0], s[1], b.mass, b.radius)
+    sc = max(np.abs(xf).max(), np.abs(yf).max())
+    assert np.abs(fx[rows] - xf).max() <= 1e-10 * sc and np.abs(fy[rows] - yf).max() <= 1e-10 * sc
+    print("n=%d: %d sampled rows, max |dF| / max|F| = %.2e" % (n, len(rows), max(np.abs(fx[rows] - xf).max(), np.abs(fy[rows] - yf).max()) / sc))
+
+
+@pytest.mark.parametrize("n,steps", [(65536, 200), (262144, 50)])
+def test_baseline_configs_3_and_4_sampled_trajectory_against_oracle(nb, oracle, n, steps):
+    """Every step of BASELINE configs 3 and 4 at FULL size against the reference's math without O(N^2) CPU work per
+    step: each step the oracle computes the pair-force sums of a sample of bodies (block-boundary slots of the
+    cell order + random ones) from the GPU's current positions, advances those bodies with the oracle's
+    compute_velocities / compute_positions, and the GPU's next state must agree on them: forces 1e-8 max|F|,
+    velocities 1e-10, positions 1e-12 (the stated fast-mode tolerance)."""
+    b = oracle.init_bodies(n)
+    g = make(nb, b, mode=nb.MODE_FAST)
+    assert g.describe()["cell_order"] is True
+    order = oracle.cell_order(nb, b.x, b.y)
+    rng = np.random.default_rng(7)
+    edge = oracle.block_sample(order, per_block_extra=0)
+    rows = np.unique(np.concatenate([rng.choice(edge, 40, replace=False), rng.integers(0, n, 24),
+                                     order[[0, 511, 512, n - 1]]])).astype(np.int32)
+    x, y, xv, yv = b.x.copy(), b.y.copy(), b.xv.copy(), b.yv.copy()
+    worst = dict(pos=0.0, vel=0.0, frc=0.0)
+    for step in range(steps):
+        xf, yf = oracle.forces_for(rows, x, y, b.mass, b.radius)
+        xn, yn, xvn, yvn = oracle.step_bodies(rows, x, y, xv, yv, xf, yf, b.mass)
+        g.step(1)
+        x, y, gxf, gyf, xv, yv = g.fetch()
+        fmax = max(np.abs(gxf).max(), np.abs(gyf).max())
+        worst["frc"] = max(worst["frc"], np.abs(gxf[rows] - xf).max() / fmax, np.abs(gyf[rows] - yf).max() / fmax)
+        worst["pos"] = max(worst["pos"], (np.abs(x[rows] - xn) / np.maximum(np.abs(xn), 1.0)).max(),
+                           (np.abs(y[rows] - yn) / np.maximum(np.abs(yn), 1.0)).max())
+        worst["vel"] = max(worst["vel"], (np.abs(xv[rows] - xvn) / np.maximum(np.abs(xvn), 1e-2)).max(),
+                           (np.abs(yv[rows] - yvn) / np.maximum(np.abs(yvn), 1e-2)).max())
+        assert worst["frc"] <= FRC_RTOL_OF_MAX and worst["pos"] <= POS_RTOL and worst["vel"] <= VEL_RTOL, (step, worst)
+    print("n=%d steps=%d worst one-step deviation from the oracle: %r" % (n, steps, worst))

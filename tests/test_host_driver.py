@@ -97,6 +97,56 @@ def test_run_xps_csv_shape(workdir):
 
 
 @pytest.mark.gpu
+def test_reference_experiment_sweep_script_unchanged(workdir, oracle, nb):
+    """bin/experiments.sh run UNCHANGED through the prun shim against the GPU-backed nbody-par: it
+    passes `--openmp --measure-comm --run-xps` (experiments.sh:42-46) and appends one CSV line per run
+    (nbody-par.c:954-957: SIZE,NODES,CPUS_PER_NODE,NBODIES,RTIME,COMMTIME,COMMTIME:RTIME,GFLOPS).  The shim's
+    PRUN_SHIM_MAX_RUNS stops the 144-run sweep after the first runs; NODES / CPUS_PER_NODE must come back from the
+    PRUN_ENVIRONMENT file the launcher writes, as in the reference (nbody-par.c:441-517)."""
+    script = os.path.join(oracle.REF_DIR, "bin", "experiments.sh")
+    if not os.path.exists(script):
+        pytest.skip("reference scripts not staged (oracle/_ref/bin)")
+    shutil.copy(script, workdir / "bin" / "experiments.sh")
+    out = workdir / "xps.csv"
+    for f in (out, workdir / ".prun_shim_count"):
+        if f.exists():
+            f.unlink()
+    env = _env()
+    env["PRUN_SHIM_MAX_RUNS"] = "7"
+    r = subprocess.run(["bash", "bin/experiments.sh", "1", "xps.csv", "1"], cwd=workdir, env=env, capture_output=True,
+                       text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert r.stdout.count("N_BODIES=") == 144          # the script walked its whole grid
+    lines = open(out).read().splitlines()
+    assert len(lines) == 7
+    want = [(512, 2, 1), (512, 2, 4), (512, 2, 16), (512, 4, 1), (512, 4, 4), (512, 4, 16), (512, 6, 1)]
+    gpus = nb.device_count()
+    for ln, (n, nodes, cpus) in zip(lines, want):
+        f = ln.split(",")
+        assert len(f) == 8, ln
+        size, got_nodes, got_cpus, got_n = int(f[0]), int(f[1]), int(f[2]), int(f[3])
+        rtime, comm, ratio, gflops = float(f[4]), float(f[5]), float(f[6]), float(f[7])
+        assert (got_nodes, got_cpus, got_n) == (nodes, cpus, n), ln
+        assert size == min(nodes * cpus, gpus, n), ln       # the GPUs that shared the rows
+        assert rtime > 0 and gflops > 0 and 0 <= ratio <= 1.0, ln
+        if size >= 2:
+            assert comm > 0, ln                             # device-timed exchange of the sharded step
+        else:
+            assert comm == 0, ln
+    # the sequential sweep's CSV (nbody-seq.c:488): N,rtime,gflops
+    script = os.path.join(oracle.REF_DIR, "bin", "sequential-experiments.sh")
+    shutil.copy(script, workdir / "bin" / "sequential-experiments.sh")
+    (workdir / ".prun_shim_count").unlink()
+    env["PRUN_SHIM_MAX_RUNS"] = "2"
+    r = subprocess.run(["bash", "bin/sequential-experiments.sh", "seq.csv", "1"], cwd=workdir, env=env, capture_output=True,
+                       text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = open(workdir / "seq.csv").read().splitlines()
+    assert [ln.split(",")[0] for ln in lines] == ["512", "1024"] and all(len(ln.split(",")) == 3 for ln in lines)
+    (workdir / ".prun_shim_count").unlink()
+
+
+@pytest.mark.gpu
 def test_reference_sanity_check_script_unchanged(workdir, oracle):
     script = os.path.join(oracle.REF_DIR, "bin", "nbody-sanity-check")
     if not os.path.exists(script):

@@ -127,3 +127,28 @@ def test_reference_nbody_par_reproduces_goldens(oracle, ppm, ranks, threads, fla
             b = oracle.init_bodies(n)
             oracle.run(b, steps, trig=0)
             assert out.stdout.decode() == oracle.format_state(b.x, b.y, b.xf, b.yf, b.xv, b.yv)
+
+
+@pytest.mark.parametrize("n,dims", [(32, (1024, 768)), (128, (1024, 768)), (3000, (320, 200)), (2, (64, 48))])
+def test_oracle_display_is_pinned_to_the_reference_display(oracle, tmp_path, n, dims):
+    """display() (nbody-seq.c:326-354) has no fixture in the reference, but the reference program itself makes
+    one: with secs_per_update = 1 and one step it paints exactly once, after step 1, into the mmapped P6 file
+    (`lastup` starts at 0: nbody-seq.c:389,467-471).  The pixels it wrote must equal oracle_display() of the
+    oracle's state after one step (libm trig, like the reference binary) -- which pins the restatement the CUDA
+    rasteriser is tested against (tests/test_gpu_parity.py::test_render_matches_reference_display)."""
+    exe = oracle.ref_binary("nbody-seq")
+    if exe is None:
+        pytest.skip("oracle/_ref/nbody-seq not built")
+    xdim, ydim = dims
+    ppm = str(tmp_path / "paint.ppm")
+    oracle.write_ppm(ppm, xdim, ydim)
+    hdr = b"P6\n%d %d\n255\n" % (xdim, ydim)
+    subprocess.run([exe, str(n), "1", ppm, "1"], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    data = open(ppm, "rb").read()
+    assert data.startswith(hdr) and len(data) == len(hdr) + xdim * ydim * 3
+    painted = np.frombuffer(data[len(hdr):], dtype=np.uint8).reshape(ydim, xdim, 3)
+    b = oracle.init_bodies(n, xdim, ydim)
+    oracle.run(b, 1, trig=0, xdim=xdim, ydim=ydim)
+    ref = oracle.display(b, xdim, ydim)
+    assert painted.any()
+    assert np.array_equal(painted, ref)
