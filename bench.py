@@ -24,8 +24,8 @@ right after the timed one: nbody_gpu_step_profiled, plain launches with an event
 peak = the DFMA rate measured live by nbody_gpu_fp64_peak (MEASURED_PEAKS.json has
 no FP64 figure).  pipe_frac = FP64-pipe instructions actually issued per pair (SASS count,
 confirmed by ncu sm__inst_executed_pipe_fp64) x pairs/s / (peak/2): the utilisation figure the
-north star's "% of FP64 pipe peak" means (an IEEE-grade rsqrt makes one unordered pair 19 pipe
-instructions = 9.5 per interaction, so the algorithmic-flop fraction cannot approach 1).
+north star's "% of FP64 pipe peak" means (the reciprocal square root makes one unordered pair 18 pipe
+instructions = 9 per interaction -- 16 = 8 in far-field tiles -- so the algorithmic-flop fraction cannot approach 1).
 traffic = DRAM bytes per force-kernel launch from the committed ncu captures (profiles/r2_traffic.json,
 written by tools/ncu_traffic.py from the .ncu-rep), keyed by kernel, N and GPU count.
 
@@ -360,7 +360,7 @@ def other_configs(nb, local_rank, peak_tf):
                                  "checked_by": "tests/test_gpu_parity.py::test_exact_4096_config2_prefix_and_graph_independence"}
     wall, dev, d, far = run(65536, nb.MODE_FAST, 200)
     rate = 200 * 65536 * 65535.0 / dev
-    ipp = 9.5 * (1.0 - far) + 8.5 * far
+    ipp = 9.0 * (1.0 - far) + 8.0 * far
     out["c3_65536x200_fast"] = {"seconds": wall, "ms_per_step": dev * 1e3 / 200, "steps_per_s": 200 / wall, "kernel": d["kernel"],
                                 "pair_interactions_per_s": rate, "far_field_fraction": far,
                                 "pipe_frac": ipp * rate / (peak_tf * 1e12 / 2.0),
@@ -451,6 +451,13 @@ def main():
         clocks["per_rank_samples"] = [int(r[2]) for r in per_rank]
         if any(r[3] > 0 for r in per_rank) and not clocks.get("reasons"):
             clocks["reasons"] = ["see other ranks"]
+    per_rank_phase = None
+    if dist is not None:
+        mine_ph = torch.tensor([prof["force"], prof["integrate"], prof["exchange"], t_ms], dtype=torch.float64, device="cuda")
+        all_ph = [torch.zeros_like(mine_ph) for _ in range(world)]
+        dist.all_gather(all_ph, mine_ph)
+        per_rank_phase = {"force": [float(t[0]) / args.steps for t in all_ph], "integrate": [float(t[1]) / args.steps for t in all_ph],
+                          "exchange": [float(t[2]) / args.steps for t in all_ph], "graph_pass": [float(t[3]) / args.steps for t in all_ph]}
     t_ms = maxreduce(t_ms)
     prof_ms = maxreduce(prof["total"])
     force_ms = maxreduce(prof["force"])
@@ -467,9 +474,23 @@ def main():
             nb.pin_host(a)                     # allocated once, page-locked once (nbody_gpu_pin_host)
         x, y, xf, yf, xv, yv = host
         e_steps = max(2, min(args.steps, 5))
+        # Multi-rank with the peer-memory exchange: every rank keeps ITS rows on the host, like the reference's ranks
+        # between two MPI_Allgatherv calls (nbody-par.c:225-263): set_state uploads the rank's own rows (the library
+        # stores them into every GPU), fetch_range brings the rank's own rows back.  The whole state still crosses
+        # PCIe both ways every step, an N-th per rank.  Otherwise (one GPU, NCCL exchange) every rank moves all of it.
+        own_rows = world > 1 and "peer-memory" in g.describe().get("exchange", "")
+        lo, hi = nb.partition(n, world, rank) if own_rows else (0, n)
+        mine = [a[lo:hi] for a in host]
+
+        def fetch_mine():
+            if own_rows:
+                g.fetch_range(lo, hi - lo, out=mine)
+            else:
+                g.fetch(out=host)
+
         g.set_state(x, y, xv, yv)              # untimed round: first-touch of the pinned pages
         g.step(1)
-        g.fetch(out=host)
+        fetch_mine()
         barrier()
         t0 = time.perf_counter()
         split = [0.0, 0.0, 0.0]
@@ -479,7 +500,7 @@ def main():
             tb = time.perf_counter()
             g.step(1)
             tc = time.perf_counter()
-            g.fetch(out=host)                  # D2H: the six columns the reference prints (waits for the step)
+            fetch_mine()                       # D2H: the six columns the reference prints (waits for the step)
             td = time.perf_counter()
             split[0] += tb - ta
             split[1] += tc - tb
@@ -493,7 +514,14 @@ def main():
                        "page-locked once with nbody_gpu_pin_host",
                "rank0_ms_per_step": {"set_state": 1e3 * split[0] / e_steps, "step_enqueue": 1e3 * split[1] / e_steps,
                                      "fetch_incl_wait_for_step": 1e3 * split[2] / e_steps},
-               "h2d_bytes_per_step_per_rank": (4 * 8 * n) // world if "peer-memory" in g.describe().get("exchange", "") else 4 * 8 * n}
+               "h2d_bytes_per_step_per_rank": 4 * 8 * (hi - lo), "d2h_bytes_per_step_per_rank": 6 * 8 * (hi - lo),
+               "rows_per_rank": "own rows [lo, hi) of nbody_gpu_partition on every rank (set_state + fetch_range)" if own_rows
+               else "all rows on every rank (set_state + fetch)"}
+        if own_rows:
+            # the pieces the ranks fetched are one consistent state: rank 0 also fetches everything and the hashes of its
+            # own slice must agree (cheap, untimed)
+            full = g.fetch()
+            e2e["own_rows_consistent_with_full_fetch"] = bool(all(np.array_equal(f[lo:hi], m) for f, m in zip(full, mine)))
 
     # ---- multi-rank parity: the sharded handle against one GPU, bit for bit, on every rank ---
     parity = None
@@ -529,8 +557,8 @@ def main():
     algo_tflops = 10.0 * launch_pairs / launch_s / 1e12   # reference flop model: 10 per directed pair
     ipp = desc.get("fp64_instr_per_pair") or None
     if ipp and far > 0.0:
-        # far-field tiles issue 17 FP64-pipe instructions per unordered pair instead of 19 (forces_sym.cuh)
-        ipp = ipp * (1.0 - far) + 8.5 * far
+        # far-field tiles issue 16 FP64-pipe instructions per unordered pair instead of 18 (forces_sym.cuh)
+        ipp = ipp * (1.0 - far) + 8.0 * far
     traffic, traffic_source = load_traffic(desc["kernel"], n, world)
     roofline = {"bound": "fp64", "achieved": algo_tflops, "peak": peak_tf, "unit": "TFLOP/s",
                 "frac": algo_tflops / peak_tf, "traffic": traffic, "traffic_source": traffic_source,
@@ -586,6 +614,8 @@ def main():
             "phase_ms_per_step": {"force": force_ms / args.steps, "integrate": integ_ms / args.steps,
                                   "exchange": exch_ms / args.steps, "whole_step_plain_launches": prof_ms / args.steps},
             "clocks": clocks, "gpu_launches": launches, "roofline": roofline}
+    if per_rank_phase:
+        line["phase_ms_per_step_per_rank"] = per_rank_phase
     if e2e:
         line["e2e"] = e2e
     if parity:

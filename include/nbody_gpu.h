@@ -129,6 +129,13 @@ int nbody_gpu_forces(nbody_gpu *h, double *xf, double *yf);
 int nbody_gpu_fetch(nbody_gpu *h, double *x, double *y, double *xf, double *yf,
                     double *xv, double *yv);
 
+/* nbody_gpu_fetch for the bodies [first, first + count) only: the arrays have `count` elements.  A rank of a
+ * multi-process job that keeps its own rows on the host (nbody_gpu_partition), like the reference's ranks between
+ * two MPI_Allgatherv calls, fetches just those -- the same collective rules as nbody_gpu_fetch apply: every rank
+ * calls it, with the same arrays NULL or non-NULL. */
+int nbody_gpu_fetch_range(nbody_gpu *h, int first, int count, double *x, double *y, double *xf, double *yf,
+                          double *xv, double *yv);
+
 /* Replaces display() (nbody-seq.c:326-354; dead code in nbody-par.c:674-702): paints the CURRENT positions
  * into rgb (xdim*ydim*3 bytes, host, row-major, 3 bytes per pixel): the first (lowest-index) body whose
  * disc of radius R+0.5 covers the pixel gives the tint, empty space is black.  Headless: a device buffer,

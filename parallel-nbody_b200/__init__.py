@@ -64,6 +64,7 @@ def lib():
     L.nbody_gpu_step_profiled.argtypes = [vp, ci, ci, ctypes.POINTER(ctypes.c_float)]
     L.nbody_gpu_forces.argtypes = [vp, _dp, _dp]
     L.nbody_gpu_fetch.argtypes = [vp] + [odp] * 6
+    L.nbody_gpu_fetch_range.argtypes = [vp, ci, ci] + [odp] * 6
     L.nbody_gpu_render.argtypes = [vp, np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")]
     L.nbody_gpu_far_fraction.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     L.nbody_gpu_sync.argtypes = [vp]
@@ -219,6 +220,18 @@ class NBodyGPU:
                 if a.dtype != np.float64 or a.shape != (self.n,) or not a.flags.c_contiguous:
                     raise ValueError("fetch(out=...) needs six contiguous float64 arrays of length n")
         _check(lib().nbody_gpu_fetch(self._h, *[a.ctypes.data_as(ctypes.c_void_p) for a in out]))
+        return tuple(out)
+
+    def fetch_range(self, first, count, out=None):
+        """fetch() for the bodies [first, first + count) only: six arrays of length count."""
+        if out is None:
+            out = [np.empty(count) for _ in range(6)]
+        else:
+            out = list(out)
+            for a in out:
+                if a.dtype != np.float64 or a.shape != (count,) or not a.flags.c_contiguous:
+                    raise ValueError("fetch_range(out=...) needs six contiguous float64 arrays of length count")
+        _check(lib().nbody_gpu_fetch_range(self._h, int(first), int(count), *[a.ctypes.data_as(ctypes.c_void_p) for a in out]))
         return tuple(out)
 
     def render(self, xdim, ydim):

@@ -25,6 +25,10 @@
 
 #include "forces_fast.cuh"
 
+#ifndef NBODY_SYM_RSQRT_ORDER
+#define NBODY_SYM_RSQRT_ORDER 2   // order of the rsqrt correction in the symmetric pair (2 or 3)
+#endif
+
 namespace nbody {
 
 struct SymBody {
@@ -68,10 +72,16 @@ __device__ __forceinline__ void pair_sym(SymBody &b, double xj, double yj, doubl
     }
     const double y0 = (FLAVOR & 1) ? rsqrt_seed_donor(q, f2) : rsqrt_seed(q);
     const double t = q * y0;
-    const double e = fma(-t, y0, 1.0);
-    const double p = fma(e, 0.375, 0.5);
+    const double e = fma(-t, y0, 1.0);       // 1 - q*y0^2, |e| <= 2^-21.9 (the seed is good to 2^-22.9)
     const double ye = y0 * e;
-    const double y1 = fma(ye, p, y0);        // 1 / (forced * sqrt(dsqr))
+#if NBODY_SYM_RSQRT_ORDER >= 3
+    const double p = fma(e, 0.375, 0.5);
+    const double y1 = fma(ye, p, y0);        // y0*(1 + e/2 + 3e^2/8) = 1 / (forced * sqrt(dsqr)) to ~1e-16
+#else
+    // y0*(1 + e/2): the dropped term 3e^2/8 <= 2.4e-14 relative, 4e5 times inside the stated force tolerance
+    // (1e-8 max|F|) and one FP64-pipe instruction per pair cheaper (DESIGN.md section 4 has the measured error table)
+    const double y1 = fma(ye, 0.5, y0);
+#endif
     const double zi = mj * y1;
     b.ax = fma(zi, dx, b.ax);
     b.ay = fma(zi, dy, b.ay);
@@ -201,9 +211,20 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int warp = tid >> 5;
-    // grid = (owned row blocks, chunks): CTAs are dispatched chunk by chunk, the short chunks (ChunkMap) last
-    const int bx = blockIdx.x, by = blockIdx.y;
-    const int blk = sym_owned_block(bx, a.v0, a.nv);               // row block index
+    // grid = the live (chunk, row block) items, chunk-major: CTAs are dispatched chunk by chunk, the short chunks
+    // (ChunkMap) last, and no CTA is launched for a chunk that lies entirely below its row block
+    int by;
+    {
+        const int c = static_cast<int>(blockIdx.x);
+        int lo = 0, hi = a.cm.nsplit;   // largest s with cta_prefix[s] <= c
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (a.cta_prefix[mid] <= c) lo = mid;
+            else hi = mid;
+        }
+        by = lo;
+    }
+    const int blk = a.owned_sorted[static_cast<int>(blockIdx.x) - a.cta_prefix[by]];   // row block index
     const int i0 = blk * SYM_RB;
     const int i1 = min(a.n, i0 + SYM_RB);
     const int jc0 = chunk_start(a.cm, by);
@@ -299,10 +320,11 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
                 // gap between the boxes against the largest r_i + r_j, in the pair's own operations:
                 // dx >= gx and dy >= gy for every pair, rounding is monotone, so dsqr >= gap2 >= md2 >= mindsqr
                 const double *tb = s_box + st * SYM_BOX_DOUBLES;
-                const double gx = fmax(0.0, fmax(tb[0] - s_bbox[2], s_bbox[0] - tb[2]));
-                const double gy = fmax(0.0, fmax(tb[1] - s_bbox[3], s_bbox[1] - tb[3]));
+                const double *rb = s_bbox;
+                const double gx = fmax(0.0, fmax(tb[0] - rb[2], rb[0] - tb[2]));
+                const double gy = fmax(0.0, fmax(tb[1] - rb[3], rb[1] - tb[3]));
                 const double gap2 = fma(gx, gx, gy * gy);
-                const double md = s_bbox[4] + tb[4];
+                const double md = rb[4] + tb[4];
                 far = gap2 >= md * md;
             }
             if (far) {

@@ -30,16 +30,16 @@ void launch_integrate_fast(const IntegrateArgs &a, cudaStream_t st)
 // order): 64 threads x 8 bodies (2 warps per CTA; one LDS pair, one accumulator rotation and one address update
 // serve 8 pairs) from SYM_WIDE_N bodies on, 128 x 4 below (more, shorter CTAs: better tail at N = 65536).
 // NBODY_DEV builds can pin either shape with NBODY_SYM_VARIANT=1|2 for A/B timing.
-int launch_forces_sym(const SymArgs &a, int nblocks_here, cudaStream_t st)
+int launch_forces_sym(const SymArgs &a, int nitems, cudaStream_t st)
 {
-    if (nblocks_here <= 0) return 0;
+    if (nitems <= 0) return 0;
     bool wide = a.n >= SYM_WIDE_N;
 #ifdef NBODY_DEV
     static const int env_variant = getenv("NBODY_SYM_VARIANT") ? atoi(getenv("NBODY_SYM_VARIANT")) : 0;
     if (env_variant == 1) wide = false;
     if (env_variant == 2) wide = true;
 #endif
-    const dim3 grid(nblocks_here, a.cm.nsplit);
+    const dim3 grid(nitems);
     static bool attr_set_dev[64] = {};   // the attribute is per device
     int dev = 0;
     cudaGetDevice(&dev);

@@ -85,7 +85,8 @@ __global__ void __launch_bounds__(256) gather_planar_kernel(const GatherArgs g)
 {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= g.n) return;
-    const int o = g.orig ? g.orig[s] : s;
+    const int o = (g.orig ? g.orig[s] : s) - g.first;
+    if (o < 0 || o >= g.count) return;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         if (g.src[k]) {

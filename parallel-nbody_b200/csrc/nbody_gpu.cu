@@ -103,6 +103,9 @@ struct Shard {
     int *p2p_err = nullptr;      // set by a barrier kernel that timed out
     std::vector<void *> ipc_opened;
     int nblocks_owned = 0;       // colpart slots (row blocks of the owned virtual ranks, whole groups)
+    int *cta_prefix = nullptr;   // symmetric kernel: work items before each chunk (SymArgs)
+    int *owned_sorted = nullptr; // symmetric kernel: owned row blocks, ascending
+    int sym_items = 0;           // symmetric kernel: grid size
     NcclComm comm = nullptr;
     cudaGraphExec_t graph[2] = {nullptr, nullptr};   // indexed by the starting slot
 };
@@ -201,6 +204,41 @@ static ChunkMap choose_split_sym(int n, int requested)
     return m;
 }
 
+// Work items of the symmetric kernel for a device that owns virtual ranks [v0, v0 + nv): its row blocks ascending, and
+// for every chunk the number of items before it; chunk s pairs with the owned blocks that start below its end.
+static void sym_work_items(int n, const ChunkMap &cm, int v0, int nv, std::vector<int> *owned, std::vector<int> *prefix)
+{
+    const int nblocks = (n + SYM_RB - 1) / SYM_RB;
+    owned->clear();
+    for (int B = 0; B < nblocks; ++B) {
+        const int v = sym_vrank(B);
+        if (v >= v0 && v < v0 + nv) owned->push_back(B);
+    }
+    prefix->assign(static_cast<size_t>(cm.nsplit) + 1, 0);
+    size_t live = 0;
+    for (int s = 0; s < cm.nsplit; ++s) {
+        long long end = static_cast<long long>(chunk_start(cm, s)) + chunk_len(cm, s);
+        if (end > n) end = n;
+        while (live < owned->size() && static_cast<long long>((*owned)[live]) * SYM_RB < end) ++live;
+        (*prefix)[s + 1] = (*prefix)[s] + static_cast<int>(live);
+    }
+}
+
+static int upload_sym_items(Shard &s, int n, const ChunkMap &cm, int v0, int nv)
+{
+    std::vector<int> owned, prefix;
+    sym_work_items(n, cm, v0, nv, &owned, &prefix);
+    if (s.cta_prefix) cudaFree(s.cta_prefix);
+    if (s.owned_sorted) cudaFree(s.owned_sorted);
+    s.cta_prefix = s.owned_sorted = nullptr;
+    NB_CUDA(cudaMalloc(&s.cta_prefix, sizeof(int) * prefix.size()));
+    NB_CUDA(cudaMalloc(&s.owned_sorted, sizeof(int) * (owned.empty() ? 1 : owned.size())));
+    NB_CUDA(cudaMemcpy(s.cta_prefix, prefix.data(), sizeof(int) * prefix.size(), cudaMemcpyHostToDevice));
+    if (!owned.empty()) NB_CUDA(cudaMemcpy(s.owned_sorted, owned.data(), sizeof(int) * owned.size(), cudaMemcpyHostToDevice));
+    s.sym_items = prefix.back();
+    return NBODY_GPU_OK;
+}
+
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 static ArenaLayout arena_layout(int npad, bool symmetric, bool sorted, int n)
@@ -236,6 +274,8 @@ static void free_shard(Shard &s)
     if (s.mr) cudaFree(s.mr);
     if (s.part) cudaFree(s.part);
     if (s.colpart) cudaFree(s.colpart);
+    if (s.cta_prefix) cudaFree(s.cta_prefix);
+    if (s.owned_sorted) cudaFree(s.owned_sorted);
     if (s.flush) cudaFree(s.flush);
     if (s.orig) cudaFree(s.orig);
     if (s.mr0) cudaFree(s.mr0);
@@ -354,11 +394,21 @@ static int enqueue_forces(nbody_gpu *h, Shard &s, int slot, double2 *exact_out)
         a.cm = h->cm;
         a.v0 = s.v0;
         a.nv = s.nv;
+        a.cta_prefix = s.cta_prefix;
+        a.owned_sorted = s.owned_sorted;
+#ifdef NBODY_DEV
+        // development knob (read at init, see init_impl): the work items are those of ONE virtual rank only -- what
+        // one GPU of an 8-way shard runs -- for timing and ncu on a single device; the step's results are garbage
+        if (const char *e = getenv("NBODY_DEV_VRANK")) {
+            a.v0 = atoi(e) % SYM_V;
+            a.nv = 1;
+        }
+#endif
         if (h->sorted && !h->fused_boxes) {   // shard boundaries cut through tiles: the boxes get their own launch
             launch_tile_boxes(s.pos[slot], s.mr, h->n, s.boxes, s.stream);
             h->launches[2] += 1;
         }
-        NB_LAUNCH_RC(launch_forces_sym(a, s.nblocks_owned, s.stream));
+        NB_LAUNCH_RC(launch_forces_sym(a, s.sym_items, s.stream));
     } else {
         launch_forces_fast(force_args(h, s, slot, nullptr), h->nsplit, s.stream);
     }
@@ -1133,6 +1183,15 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
                 s.nblocks_owned = static_cast<int>(slots);
                 NB_CUDA(cudaMalloc(&s.colpart, bytes * slots));
                 NB_CUDA(cudaMemsetAsync(s.colpart, 0, bytes * slots, s.stream));
+                int items_v0 = s.v0, items_nv = s.nv;
+#ifdef NBODY_DEV
+                if (const char *e = getenv("NBODY_DEV_VRANK")) {
+                    items_v0 = atoi(e) % SYM_V;
+                    items_nv = 1;
+                }
+#endif
+                const int rc_items = upload_sym_items(s, h->n, h->cm, items_v0, items_nv);
+                if (rc_items) return rc_items;
             }
             if (h->sorted) {
                 NB_CUDA(cudaMalloc(&s.orig, sizeof(int) * static_cast<size_t>(h->npad)));
@@ -1427,7 +1486,7 @@ int nbody_gpu_sync(nbody_gpu *h)
 // Up to three double2 device arrays of shard 0 (slot order) -> the caller's planar arrays (body order): one
 // gather kernel writes planar staging on the device, then one D2H copy per requested array, straight into the
 // caller's memory (full PCIe speed if it is registered, driver-staged if pageable).
-static int download(nbody_gpu *h, const double2 *const src[3], double *const out[6])
+static int download(nbody_gpu *h, const double2 *const src[3], double *const out[6], int first, int count)
 {
     Shard &s = h->shards[0];
     NB_CUDA(cudaSetDevice(s.device));
@@ -1444,10 +1503,13 @@ static int download(nbody_gpu *h, const double2 *const src[3], double *const out
     if (!any) return NBODY_GPU_OK;
     g.orig = h->sorted ? s.orig : nullptr;
     g.n = h->n;
+    g.first = first;
+    g.count = count;
     launch_gather_planar(g, s.stream);
     h->launches[2] += 1;
     for (int k = 0; k < 6; ++k)
-        if (out[k]) NB_CUDA(cudaMemcpyAsync(out[k], s.plan + k * np, sizeof(double) * h->n, cudaMemcpyDeviceToHost, s.stream));
+        if (out[k] && count > 0)
+            NB_CUDA(cudaMemcpyAsync(out[k], s.plan + k * np, sizeof(double) * count, cudaMemcpyDeviceToHost, s.stream));
     return NBODY_GPU_OK;
 }
 
@@ -1481,15 +1543,18 @@ int nbody_gpu_forces(nbody_gpu *h, double *xf, double *yf)
     if (rc) return poison(h, rc);
     const double2 *src[3] = {nullptr, h->shards[0].fscratch, nullptr};
     double *out[6] = {nullptr, nullptr, xf, yf, nullptr, nullptr};
-    rc = download(h, src, out);
+    rc = download(h, src, out, 0, h->n);
     if (!rc) rc = sync_all(h);
     return poison(h, rc);
 }
 
-int nbody_gpu_fetch(nbody_gpu *h, double *x, double *y, double *xf, double *yf, double *xv, double *yv)
+int nbody_gpu_fetch_range(nbody_gpu *h, int first, int count, double *x, double *y, double *xf, double *yf, double *xv,
+                          double *yv)
 {
     int rc = check_usable(h);
     if (rc) return rc;
+    if (first < 0 || count < 0 || first > h->n || count > h->n - first)
+        return fail(NBODY_GPU_EINVAL, "bodies [%d, %d) are not inside [0, %d)", first, first + count, h->n);
     // forces and velocities live sharded during the run; complete them like the reference's
     // whole-struct MPI_Allgatherv leaves them (nbody-par.c:933-936)
     rc = complete_state(h, xv || yv, xf || yf);
@@ -1497,7 +1562,7 @@ int nbody_gpu_fetch(nbody_gpu *h, double *x, double *y, double *xf, double *yf, 
     Shard &s0 = h->shards[0];
     const double2 *src[3] = {s0.pos[h->cur], s0.frc, s0.vel};
     double *out[6] = {x, y, xf, yf, xv, yv};
-    rc = download(h, src, out);
+    rc = download(h, src, out, first, count);
     if (!rc) rc = sync_all(h);
     if (rc) return poison(h, rc);
     for (Shard &s : h->shards) {
@@ -1505,6 +1570,12 @@ int nbody_gpu_fetch(nbody_gpu *h, double *x, double *y, double *xf, double *yf, 
         NB_CUDA(cudaGetLastError());
     }
     return NBODY_GPU_OK;
+}
+
+int nbody_gpu_fetch(nbody_gpu *h, double *x, double *y, double *xf, double *yf, double *xv, double *yv)
+{
+    if (!h) return fail(NBODY_GPU_EINVAL, "handle is NULL");
+    return nbody_gpu_fetch_range(h, 0, h->n, x, y, xf, yf, xv, yv);
 }
 
 int nbody_gpu_describe(const nbody_gpu *h, char *buf, int len)
@@ -1515,9 +1586,9 @@ int nbody_gpu_describe(const nbody_gpu *h, char *buf, int len)
                          : h->symmetric ? (h->n >= SYM_WIDE_N ? "forces_sym_kernel<64,8>" : "forces_sym_kernel<128,4>")
                                         : "forces_fast_kernel<2,4,1,true>";
     // FP64-pipe instructions per directed pair-interaction (SASS counts): the symmetric
-    // kernel issues 19 per unordered pair = 2 interactions (17 in far-field tiles: see nbody_gpu_far_fraction);
+    // kernel issues 18 per unordered pair = 2 interactions (16 in far-field tiles: see nbody_gpu_far_fraction);
     // exact mode is not a fixed count (divisions, branches)
-    const double ipp = !fast ? 0.0 : h->symmetric ? 9.5 : 16.0;
+    const double ipp = !fast ? 0.0 : h->symmetric ? 9.0 : 16.0;
     const int graph = h->small ? 0 : ((!h->sharded || h->p2p) ? h->graph_steps : 0);
     char tmp[768];
     const int need = snprintf(tmp, sizeof tmp,
@@ -1567,6 +1638,7 @@ int nbody_gpu_far_fraction(nbody_gpu *h, double *fraction)
             b[2] = q[2] > b[2] ? q[2] : b[2]; b[3] = q[3] > b[3] ? q[3] : b[3];
             b[4] = q[4] > b[4] ? q[4] : b[4];
         }
+        const double rows = (B + 1) * SYM_RB <= h->n ? SYM_RB : h->n - B * SYM_RB;
         for (int T = (B + 1) * tiles_per_block; T < ntiles; ++T) {
             const double *q = &bx[static_cast<size_t>(T) * SYM_BOX_DOUBLES];
             double gx = q[0] - b[2] > b[0] - q[2] ? q[0] - b[2] : b[0] - q[2];
@@ -1574,7 +1646,7 @@ int nbody_gpu_far_fraction(nbody_gpu *h, double *fraction)
             if (gx < 0.0) gx = 0.0;
             if (gy < 0.0) gy = 0.0;
             const double md = b[4] + q[4];
-            const int cnt = (T + 1) * TILE_J <= h->n ? TILE_J : h->n - T * TILE_J;
+            const double cnt = rows * ((T + 1) * TILE_J <= h->n ? TILE_J : h->n - T * TILE_J);
             all += cnt;
             if (gx * gx + gy * gy >= md * md) far += cnt;
         }

@@ -59,6 +59,11 @@ struct SymArgs {
     int npad;
     ChunkMap cm;
     int v0, nv;           // this device owns the row blocks B with (B % SYM_V) in [v0, v0+nv): "virtual ranks"
+    // The grid holds live work items only: item c = (chunk s, owned block), chunk-major.  cta_prefix[s] = items before
+    // chunk s (nsplit + 1 entries), owned_sorted = this device's row blocks ascending; chunk s pairs with the first
+    // cta_prefix[s+1] - cta_prefix[s] of them (the blocks that start below the chunk's end).
+    const int *cta_prefix;
+    const int *owned_sorted;
 };
 
 // The symmetric kernel's partial sums are combined through SYM_V fixed "virtual ranks": row block B
@@ -164,6 +169,7 @@ struct GatherArgs {                 // double2 arrays in slot order -> planar ar
     double *a[3], *b[3];
     const int *orig;                // slot -> body (nullptr = identity)
     int n;
+    int first, count;               // only bodies [first, first + count) are written, at index body - first
 };
 struct PublishArgs {                // store this device's rows of up to two sharded arrays into every peer
     const double2 *src[2];
@@ -202,7 +208,7 @@ void launch_integrate_exact(const IntegrateArgs &a, cudaStream_t st);
 void launch_forces_fast(const ForceArgs &a, int nsplit, cudaStream_t st);
 void launch_integrate_fast(const IntegrateArgs &a, cudaStream_t st);
 void launch_reduce_fast(const IntegrateArgs &a, cudaStream_t st);
-int launch_forces_sym(const SymArgs &a, int nblocks_here, cudaStream_t st);   // returns cudaError_t
+int launch_forces_sym(const SymArgs &a, int nitems, cudaStream_t st);   // returns cudaError_t
 void launch_render(const double2 *pos, const double2 *mr, int n, int xdim, int ydim, int *owner, unsigned char *rgb,
                    cudaStream_t st);
 void launch_sym_reduce(const SymReduceArgs &a, cudaStream_t st);

@@ -335,3 +335,59 @@ def test_baseline_configs_3_and_4_sampled_trajectory_against_oracle(nb, oracle, 
                            (np.abs(yv[rows] - yvn) / np.maximum(np.abs(yvn), 1e-2)).max())
         assert worst["frc"] <= FRC_RTOL_OF_MAX and worst["pos"] <= POS_RTOL and worst["vel"] <= VEL_RTOL, (step, worst)
     print("n=%d steps=%d worst one-step deviation from the oracle: %r" % (n, steps, worst))
+
+
+@pytest.mark.parametrize("n,mode,kw", [(300, 0, {}), (3000, 1, dict(symmetric=1)), (17000, 1, dict(symmetric=1, sort=1))])
+def test_fetch_range_and_forces_leave_the_state_alone(nb, oracle, n, mode, kw):
+    """nbody_gpu_fetch_range returns the same numbers as the slice of a full fetch (cell order included), rejects
+    ranges outside [0, n), and nbody_gpu_forces does not disturb what fetch returns (the LAST STEP's forces)."""
+    b = oracle.init_bodies(n)
+    g = make(nb, b, mode=mode, **kw)
+    g.step(3)
+    full = g.fetch()
+    for first, count in ((0, n), (0, 1), (n - 1, 1), (n // 3, n // 2), (5, 0)):
+        part = g.fetch_range(first, count)
+        for a, c in zip(full, part):
+            assert np.array_equal(a[first:first + count].view(np.uint64), c.view(np.uint64)), (first, count)
+    with pytest.raises(nb.NBodyGPUError):
+        g.fetch_range(n - 1, 2)
+    fx, fy = g.forces()                       # forces at the CURRENT positions: not the last step's
+    assert not np.array_equal(fx, full[2])
+    again = g.fetch()
+    for a, c in zip(full, again):
+        assert np.array_equal(a.view(np.uint64), c.view(np.uint64))
+    g.step(2)                                 # and the run goes on as if forces() had not been called
+    h = make(nb, b, mode=mode, **kw)
+    h.step(5)
+    for a, c in zip(g.fetch(), h.fetch()):
+        assert np.array_equal(a.view(np.uint64), c.view(np.uint64))
+
+
+def test_pinned_host_buffers_round_trip(nb, oracle):
+    """nbody_gpu_pin_host: set_state / fetch through page-locked caller arrays give the same bits as pageable ones."""
+    n = 20000
+    b = oracle.init_bodies(n)
+    g = make(nb, b, mode=nb.MODE_FAST)
+    g.step(2)
+    plain = g.fetch()
+    host = [np.empty(n) for _ in range(6)]
+    for a in host:
+        nb.pin_host(a)
+    try:
+        g.fetch(out=host)
+        for a, c in zip(plain, host):
+            assert np.array_equal(a.view(np.uint64), c.view(np.uint64))
+        g.set_state(host[0], host[1], host[4], host[5])
+        g.step(2)
+        pinned = g.fetch(out=host)
+        h = make(nb, b, mode=nb.MODE_FAST)
+        h.step(2)
+        mid = h.fetch()
+        h.set_state(mid[0], mid[1], mid[4], mid[5])
+        h.step(2)
+        for a, c in zip(pinned, h.fetch()):
+            assert np.array_equal(a.view(np.uint64), c.view(np.uint64))
+    finally:
+        g.sync()
+        for a in host:
+            nb.unpin_host(a)
