@@ -26,7 +26,18 @@
 #include "forces_fast.cuh"
 
 #ifndef NBODY_SYM_RSQRT_ORDER
-#define NBODY_SYM_RSQRT_ORDER 2   // order of the rsqrt correction in the symmetric pair (2 or 3)
+#define NBODY_SYM_RSQRT_ORDER 2   // order of the rsqrt correction in this kernel's pairs (2 or 3)
+#endif
+// Second order: y1 = y0*(1 + e/2), e = 1 - q*y0^2.  The dropped term 3e^2/8 is one-sided (every pair term comes out too
+// small); its mean over the seed's error distribution is a property of the seed unit (MUFU.RSQ64H with the low word
+// taken from a dead register, rsqrt_seed_donor), measured on both BASELINE workloads as 1.94e-13 (N = 65536:
+// 1.92e-13, N = 262144: 1.97e-13; profiles/r2_error_table.log).  The kernel multiplies its sums by G anyway: folding
+// (1 + that mean) into the constant makes the pair terms unbiased at no cost, and the error of a body's force
+// drops from the bias (2e-13) to the zero-mean scatter.
+#if NBODY_SYM_RSQRT_ORDER >= 3
+#define NBODY_SYM_G NB_GRAVITY
+#else
+#define NBODY_SYM_G (NB_GRAVITY * (1.0 + 1.94e-13))
 #endif
 
 namespace nbody {
@@ -38,7 +49,7 @@ struct SymBody {
 };
 
 // MUFU.RSQ64H reads and writes high words only; PTX's rsqrt.approx.f64 also zeroes the low word, which costs a
-// move per pair.  The seed is only good to 2^-22.9, so any low word will do: take it from a value that dies
+// move per pair.  The seed is only good to 2^-20 (tools/rsqrt_seed_probe.cu), so any low word will do: take it from a value that dies
 // here (the register pair is reused in place, no move).
 __device__ __forceinline__ double rsqrt_seed_donor(double q, double donor)
 {
@@ -72,15 +83,13 @@ __device__ __forceinline__ void pair_sym(SymBody &b, double xj, double yj, doubl
     }
     const double y0 = (FLAVOR & 1) ? rsqrt_seed_donor(q, f2) : rsqrt_seed(q);
     const double t = q * y0;
-    const double e = fma(-t, y0, 1.0);       // 1 - q*y0^2, |e| <= 2^-21.9 (the seed is good to 2^-22.9)
+    const double e = fma(-t, y0, 1.0);       // 1 - q*y0^2; |e| < 4e-6 (seed: 2^-19, measured by tools/rsqrt_seed_probe.cu, + the donated low word: 2^-20)
     const double ye = y0 * e;
 #if NBODY_SYM_RSQRT_ORDER >= 3
     const double p = fma(e, 0.375, 0.5);
     const double y1 = fma(ye, p, y0);        // y0*(1 + e/2 + 3e^2/8) = 1 / (forced * sqrt(dsqr)) to ~1e-16
 #else
-    // y0*(1 + e/2): the dropped term 3e^2/8 <= 2.4e-14 relative, 4e5 times inside the stated force tolerance
-    // (1e-8 max|F|) and one FP64-pipe instruction per pair cheaper (DESIGN.md section 4 has the measured error table)
-    const double y1 = fma(ye, 0.5, y0);
+    const double y1 = fma(ye, 0.5, y0);      // y0*(1 + e/2); the mean of the dropped term is folded into NBODY_SYM_G
 #endif
     const double zi = mj * y1;
     b.ax = fma(zi, dx, b.ax);
@@ -104,13 +113,17 @@ __device__ __forceinline__ void pair_dir(SymBody &b, double xj, double yj, doubl
     b.minhi = min(b.minhi, __double2hiint(dsqr) | self);
     const double f2 = forced * forced;
     const double q = fma(f2, dsqr, 1e-290);
-    const double y0 = rsqrt_seed(q);
+    const double y0 = rsqrt_seed_donor(q, f2);   // the same seed as pair_sym: the same error distribution
     const double t = q * y0;
     const double e = fma(-t, y0, 1.0);
-    const double p = fma(e, 0.375, 0.5);
     const double z0 = mj * y0;
     const double ze = z0 * e;
+#if NBODY_SYM_RSQRT_ORDER >= 3
+    const double p = fma(e, 0.375, 0.5);
     const double s = fma(ze, p, z0);
+#else
+    const double s = fma(ze, 0.5, z0);
+#endif
     b.ax = fma(s, dx, b.ax);
     b.ay = fma(s, dy, b.ay);
 }
@@ -368,7 +381,7 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
                 const double2 pj = tp[jt];
                 const double2 qj = tm[jt];
                 if (s_flag[tile & 1]) cx += sym_col_rescan(a.pos, a.mr, i0, i1, pj.x, pj.y, qj.y);
-                const double gmj = -NB_GRAVITY * qj.x;
+                const double gmj = -NBODY_SYM_G * qj.x;
                 a.colpart[static_cast<size_t>(sym_local_block(blk, a.v0, a.nv)) * a.npad + jb + jt] = make_double2(gmj * cx, gmj * cy);
             }
             if (tid == 0) s_flag[(tile + 1) & 1] = 0;
@@ -380,7 +393,7 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
 #pragma unroll
     for (int k = 0; k < SYM_IB; ++k) {
         if (idx[k] < a.n) {
-            const double gm = NB_GRAVITY * b[k].m;
+            const double gm = NBODY_SYM_G * b[k].m;
             a.rowpart[static_cast<size_t>(by) * a.npad + idx[k]] = make_double2(gm * b[k].ax, gm * b[k].ay);
         }
     }
