@@ -181,6 +181,16 @@ void nbody_gpu_partition(int n, int nranks, int rank, int *lo, int *hi);
  * step (symmetric: each unordered pair once, directed inside a row block; else rows x n). */
 int nbody_gpu_shard_plan(int n, int mode, int nranks, int rank, int out[8], long long *pair_evaluations);
 
+/* The symmetric kernel's work items for rank `rank` of `nranks` (host arithmetic only; the library's own table):
+ * item k is CTA k of the force kernel = (row block blocks[k], j-chunk chunks[k]), in dispatch order.  Writes at most
+ * `cap` items, *count = the number there are.  Chunk s covers bodies [chunk_start[s], chunk_start[s+1]) --
+ * chunk_start (may be NULL) receives at most chunk_cap entries, *nchunks = the number of chunks.  The reaction sums
+ * of one (virtual rank, 1024-body segment) are added by that virtual rank's row blocks in ascending order, each
+ * CTA waiting for the previous one: tests check that the CTA waited for always has a lower index (it is dispatched
+ * earlier, so the wait cannot deadlock).  Returns NBODY_GPU_EINVAL when the symmetric kernel would not be used. */
+int nbody_gpu_sym_work_items(int n, int nranks, int rank, int *blocks, int *chunks, int cap, int *count,
+                             int *chunk_start, int chunk_cap, int *nchunks);
+
 /* The reference's own partition rule, for comparison (nbody-par.c:225-263):
  * counts n/P, ranks 1..n%P get one more; displacements are the prefix sum. */
 void nbody_gpu_partition_reference(int n, int nranks, int *counts, int *displs);

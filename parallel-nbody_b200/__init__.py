@@ -87,6 +87,9 @@ def lib():
     L.nbody_gpu_fp64_peak.argtypes = [ci, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
     L.nbody_gpu_abi_version.restype = ci
     L.nbody_gpu_shard_plan.argtypes = [ci, ci, ci, ci, ctypes.POINTER(ci), ctypes.POINTER(ctypes.c_longlong)]
+    ip = ctypes.POINTER(ci)
+    if not os.environ.get("NBODY_GPU_LIB") or hasattr(L, "nbody_gpu_sym_work_items"):   # an older build under A/B test may lack it
+        L.nbody_gpu_sym_work_items.argtypes = [ci, ci, ci, ip, ip, ci, ip, ip, ci, ip]
     L.nbody_gpu_pin_host.argtypes = [vp, ctypes.c_size_t]
     L.nbody_gpu_unpin_host.argtypes = [vp]
     _lib = L
@@ -128,6 +131,20 @@ def shard_plan(n, mode, nranks, rank):
     _check(lib().nbody_gpu_shard_plan(n, mode, nranks, rank, out, ctypes.byref(ev)))
     return dict(lo=out[0], hi=out[1], v0=out[2], nv=out[3], row_blocks=out[4], chunks=out[5], long_chunks=out[6],
                 symmetric=bool(out[7]), pair_evaluations=ev.value)
+
+
+def sym_work_items(n, nranks=1, rank=0):
+    """The symmetric kernel's (row block, chunk) work items of one rank in dispatch order, and the chunk boundaries:
+    (blocks, chunks, chunk_start) as int32 arrays (chunk s covers bodies chunk_start[s]..chunk_start[s+1])."""
+    count, nchunks = ctypes.c_int(), ctypes.c_int()
+    _check(lib().nbody_gpu_sym_work_items(n, nranks, rank, None, None, 0, ctypes.byref(count), None, 0, ctypes.byref(nchunks)))
+    blocks = np.empty(count.value, dtype=np.int32)
+    chunks = np.empty(count.value, dtype=np.int32)
+    start = np.empty(nchunks.value + 1, dtype=np.int32)
+    ip = ctypes.POINTER(ctypes.c_int)
+    _check(lib().nbody_gpu_sym_work_items(n, nranks, rank, blocks.ctypes.data_as(ip), chunks.ctypes.data_as(ip), count.value,
+                                          ctypes.byref(count), start.ctypes.data_as(ip), nchunks.value + 1, ctypes.byref(nchunks)))
+    return blocks, chunks, start
 
 
 def reference_init(n, xdim=1024, ydim=768):

@@ -7,16 +7,22 @@
 //   * below the block: skipped (those pairs belong to the block that owns j),
 //   * inside the block (diagonal tiles): directed evaluation, both directions, no reaction,
 //   * above the block: one evaluation per pair; +f accumulates in registers for body i
-//     (row sum) and the reaction on body j is reduced over the 32 lanes by a shuffle
-//     butterfly, over the 8 warps through shared memory, and written ONCE per (block, j) to
-//     colpart[B][j] -- no atomics, fixed order, so the result is deterministic.
+//     (row sum); the reaction on body j travels through the warp in a rotating accumulator,
+//     the warps' sums are added in warp order through shared memory and kept there for a
+//     segment of SYM_SEG bodies j.  The segment is then ADDED to vacc[v][j] (v = the block's
+//     virtual rank) -- not with atomics: the CTAs of v's row blocks take turns in ascending
+//     block order (turn[v][segment] counts them, acquire/release at GPU scope, the way a
+//     serial split-K GEMM hands its tile from CTA to CTA), so the order of the additions is
+//     fixed, the result is deterministic, and the reaction sums take nv * N * 16 B instead
+//     of one N-vector per row block.  CTAs are dispatched row block by row block, so the
+//     CTA a turn waits for started a row of CTAs earlier and has normally long finished.
 // Far field: with the bodies in cell order (sort_kernels.cuh) most (row block, j tile) pairs are further apart
 // than any r_i + r_j of their bodies.  Every tile carries a bounding box (x/y range, largest radius; one more
 // TMA copy per tile); if the gap between the block's box and the tile's box is at least rmax_B + rmax_T the
 // clamp max(dsqr, mindsqr) is the identity for every pair of the tile and no two bodies can coincide, so the
 // tile runs the far-field form of the pair: 17 FP64-pipe instructions and no integer work.  The test uses the
 // same rounded operations as the pair itself (monotone), so it is exact and both forms give the same bits.
-// sym_reduce_kernel then folds the partial sums into SYM_V per-virtual-rank vectors (step_args.h) and
+// sym_reduce_kernel then adds each body's row sums to its block's virtual rank: SYM_V per-virtual-rank vectors (step_args.h), and
 // integrate_kernel adds those in a fixed order: the same bits on 1, 2, 4 or 8 GPUs.  Per unordered pair: 19 FP64-pipe instructions (13 shared, 3 per side)
 // + 1 MUFU + ~8 ALU/LSU + 0.3 SHFL, against 2 x (16 + ...) for the directed kernel.
 #pragma once
@@ -172,8 +178,29 @@ __device__ __forceinline__ void sym_group(SymBody (&b)[IB], const double2 *tp, c
     col[g + lane] = make_double2(cx, cy);   // entries >= cnt are never read
 }
 
-constexpr int sym_smem_bytes(int threads) { return STAGES * TILE_J * 16 * 2 + (threads / 32) * TILE_J * 16 + (STAGES + 1) * SYM_BOX_DOUBLES * 8 + 64; }
+constexpr int sym_smem_bytes(int threads) { return STAGES * TILE_J * 16 * 2 + (threads / 32) * TILE_J * 16 + SYM_SEG * 16 + (STAGES + 1) * SYM_BOX_DOUBLES * 8 + 64; }
 static_assert(SYM_RB % TILE_J == 0, "row blocks must be tile aligned");
+static_assert(SYM_SEG % TILE_J == 0 && SYM_SEG % SYM_RB == 0, "segments are whole tiles and whole row blocks");
+
+// A CTA's turn in its (virtual rank, segment) chain: wait until the `seq` blocks before it have added their sums.
+// The CTA waited for has a lower blockIdx (dispatched earlier), so it is running or done; the wait still gives up
+// after ~4 s (a lost predecessor must not hang the device) and raises the error word.
+__device__ __forceinline__ void turn_wait(const int *turn, int seq, int *error_word)
+{
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(turn) : "memory");
+    if (v == seq) return;
+    for (unsigned spins = 0; spins < (1u << 24); ++spins) {
+        __nanosleep(spins < 64 ? 32 : 256);
+        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(turn) : "memory");
+        if (v == seq) return;
+    }
+    atomicExch(error_word, SYM_ERR_TURN);
+}
+__device__ __forceinline__ void turn_pass(int *turn, int next)
+{
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(turn), "r"(next) : "memory");
+}
 
 // Rare path, row side of a tile above the block (all j > i): + m_j / mindsqr for coincident j.
 __device__ __noinline__ double sym_row_rescan(const double2 *s_pos, const double2 *s_mr, int cnt, double xi, double yi,
@@ -216,7 +243,8 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     double2 *s_pos = reinterpret_cast<double2 *>(sym_smem);                 // [STAGES][TILE_J]
     double2 *s_mr = s_pos + STAGES * TILE_J;                                // [STAGES][TILE_J]
     double2 *s_col = s_mr + STAGES * TILE_J;                                // [SYM_WARPS][TILE_J]
-    double *s_box = reinterpret_cast<double *>(s_col + SYM_WARPS * TILE_J);   // [STAGES][SYM_BOX_DOUBLES] tile boxes
+    double2 *s_seg = s_col + SYM_WARPS * TILE_J;                            // [SYM_SEG] reaction sums of the current segment
+    double *s_box = reinterpret_cast<double *>(s_seg + SYM_SEG);              // [STAGES][SYM_BOX_DOUBLES] tile boxes
     double *s_bbox = s_box + STAGES * SYM_BOX_DOUBLES;                        // [SYM_BOX_DOUBLES] this row block's box
     uint64_t *s_full = reinterpret_cast<uint64_t *>(s_bbox + SYM_BOX_DOUBLES);
     int *s_flag = reinterpret_cast<int *>(s_full + STAGES);                 // [2] coincidence flags
@@ -224,20 +252,11 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int warp = tid >> 5;
-    // grid = the live (chunk, row block) items, chunk-major: CTAs are dispatched chunk by chunk, the short chunks
-    // (ChunkMap) last, and no CTA is launched for a chunk that lies entirely below its row block
-    int by;
-    {
-        const int c = static_cast<int>(blockIdx.x);
-        int lo = 0, hi = a.cm.nsplit;   // largest s with cta_prefix[s] <= c
-        while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (a.cta_prefix[mid] <= c) lo = mid;
-            else hi = mid;
-        }
-        by = lo;
-    }
-    const int blk = a.owned_sorted[static_cast<int>(blockIdx.x) - a.cta_prefix[by]];   // row block index
+    // grid = the live (row block, chunk) items in dispatch order (SymArgs::items): no CTA is launched for a chunk that
+    // lies entirely below its row block
+    const int2 item = a.items[blockIdx.x];
+    const int blk = item.x;   // row block index
+    const int by = item.y;    // chunk index
     const int i0 = blk * SYM_RB;
     const int i1 = min(a.n, i0 + SYM_RB);
     const int jc0 = chunk_start(a.cm, by);
@@ -245,6 +264,10 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     const int j0 = max(jc0, i0);            // tiles below the block are not ours (tile aligned: chunks and blocks are)
     if (i0 >= a.n || j0 >= j1) return;      // block beyond the last body, or whole chunk below the block
     const int ntiles = (j1 - j0 + TILE_J - 1) / TILE_J;
+    // this CTA's place in the reaction-sum chains of its virtual rank
+    const int vloc = sym_vrank(blk) - a.v0;
+    const int seq = sym_vrank_seq(blk);
+    const int seg0 = by < a.cm.nbig ? by * segs_per_chunk(a.cm) : a.cm.nbig * segs_per_chunk(a.cm) + (by - a.cm.nbig);
 
     if (tid == 0) {
         for (int s = 0; s < STAGES; ++s) mbar_init(&s_full[s], 1);
@@ -382,12 +405,39 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
                 const double2 qj = tm[jt];
                 if (s_flag[tile & 1]) cx += sym_col_rescan(a.pos, a.mr, i0, i1, pj.x, pj.y, qj.y);
                 const double gmj = -NBODY_SYM_G * qj.x;
-                a.colpart[static_cast<size_t>(sym_local_block(blk, a.v0, a.nv)) * a.npad + jb + jt] = make_double2(gmj * cx, gmj * cy);
+                s_seg[(jb - jc0) % SYM_SEG + jt] = make_double2(gmj * cx, gmj * cy);
             }
             if (tid == 0) s_flag[(tile + 1) & 1] = 0;
             __syncthreads();
         }
         if (tid == 0 && tile + STAGES < ntiles) issue(tile + STAGES);
+        // last tile of a segment: add the segment's reaction sums to vacc when it is this block's turn.  Only the
+        // part above the block carries sums (a segment that ends with the block itself has none: nothing to add,
+        // and no later block of the chain either).
+        {
+            const int segi = (jb - jc0) / SYM_SEG;
+            const int sstart = jc0 + segi * SYM_SEG;
+            const int send = min(j1, sstart + SYM_SEG);
+            const int lo = max(sstart, i0 + SYM_RB);
+            if (jb + TILE_J >= send && lo < send) {   // block-uniform
+                int *turn = a.turn + static_cast<size_t>(vloc) * a.nseg + seg0 + segi;
+                if (tid == 0) turn_wait(turn, seq, a.error_word);
+                __syncthreads();
+                double2 *acc = a.vacc + static_cast<size_t>(vloc) * a.npad;
+                for (int j = lo + tid; j < send; j += SYM_THREADS) {
+                    double2 t = __ldcg(acc + j);   // L2: the line may sit stale in this SM's L1 from an earlier CTA
+                    const double2 c = s_seg[j - sstart];
+                    t.x += c.x;
+                    t.y += c.y;
+                    __stcg(acc + j, t);
+                }
+                __syncthreads();
+                if (tid == 0) {
+                    __threadfence();
+                    turn_pass(turn, seq + 1);
+                }
+            }
+        }
     }
 
 #pragma unroll
@@ -399,6 +449,17 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     }
 }
 
+// The force kernel's reaction sum for (local virtual rank vl, body j); leaves vacc and the turn counts zero for
+// the next launch.
+__device__ __forceinline__ double2 sym_take_reactions(const SymReduceArgs &a, int j, int vl)
+{
+    double2 *p = a.vacc + static_cast<size_t>(vl) * a.npad + j;
+    const double2 r = *p;
+    *p = make_double2(0.0, 0.0);
+    if (j < a.nseg) a.turn[static_cast<size_t>(vl) * a.nseg + j] = 0;
+    return r;
+}
+
 // vbuf[v][j] for the virtual ranks this device owns, one thread per (j, v).
 __global__ void __launch_bounds__(128) sym_reduce_kernel(const SymReduceArgs a)
 {
@@ -406,18 +467,8 @@ __global__ void __launch_bounds__(128) sym_reduce_kernel(const SymReduceArgs a)
     if (j >= a.n) return;
     const int v = a.v0 + blockIdx.y;
     const int blk = j / SYM_RB;
-    double xf = 0.0, yf = 0.0;
-    for (int g0 = 0; g0 < blk; g0 += 2 * SYM_V) {   // v's blocks below block(j), B ascending: 16g+v, 16g+15-v
-        const int Bs[2] = {g0 + v, g0 + 2 * SYM_V - 1 - v};
-#pragma unroll
-        for (int q = 0; q < 2; ++q) {
-            if (Bs[q] < blk) {
-                const double2 t = a.colpart[static_cast<size_t>(sym_local_block(Bs[q], a.v0, a.nv)) * a.npad + j];
-                xf += t.x;
-                yf += t.y;
-            }
-        }
-    }
+    const double2 r = sym_take_reactions(a, j, blockIdx.y);   // v's blocks below block(j), B ascending
+    double xf = r.x, yf = r.y;
     if (sym_vrank(blk) == v) {                // j's own row sums, chunk ascending
         for (int s = chunk_of(a.cm, blk * SYM_RB); s < a.cm.nsplit; ++s) {
             const double2 t = a.rowpart[static_cast<size_t>(s) * a.npad + j];

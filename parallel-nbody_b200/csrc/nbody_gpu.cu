@@ -82,7 +82,10 @@ struct Shard {
     unsigned long long *epoch = nullptr;   // [P2P_PHASES] this device's own barrier counts
     double2 *mr = nullptr;
     double2 *part = nullptr;
-    double2 *colpart = nullptr;  // symmetric fast kernel: reaction partial sums [owned blocks][npad]
+    double2 *vacc = nullptr;     // symmetric fast kernel: reaction sums per owned virtual rank [nv][npad] (SymArgs)
+    int *turn = nullptr;         // symmetric fast kernel: [nv][nseg] blocks that have added their reaction sums
+    int nseg = 0;
+    int *sym_err = nullptr;      // device error word: a force-kernel CTA gave up waiting for its turn (SYM_ERR_TURN)
     // cell order + far-field test of the symmetric kernel (kernels_sort.cu)
     int *orig = nullptr;         // original index of slot s (identity until the first sort)
     double2 *mr0 = nullptr;      // (mass, radius) in original order, for set_state
@@ -100,11 +103,9 @@ struct Shard {
     std::vector<cudaEvent_t> prof_ev;   // [PROF_CHUNK][6] phase events of nbody_gpu_step_profiled
     int v0 = 0, nv = SYM_V;      // virtual ranks owned by this shard
     PeerTable peers = {};        // fused peer-memory exchange (npeers = 0: not in use)
-    int *p2p_err = nullptr;      // set by a barrier kernel that timed out
+    int *p2p_err = nullptr;      // = sym_err: ... or a barrier kernel timed out (1 + phase)
     std::vector<void *> ipc_opened;
-    int nblocks_owned = 0;       // colpart slots (row blocks of the owned virtual ranks, whole groups)
-    int *cta_prefix = nullptr;   // symmetric kernel: work items before each chunk (SymArgs)
-    int *owned_sorted = nullptr; // symmetric kernel: owned row blocks, ascending
+    int2 *items = nullptr;       // symmetric kernel: (row block, chunk) work items in dispatch order (SymArgs)
     int sym_items = 0;           // symmetric kernel: grid size
     NcclComm comm = nullptr;
     cudaGraphExec_t graph[2] = {nullptr, nullptr};   // indexed by the starting slot
@@ -204,38 +205,37 @@ static ChunkMap choose_split_sym(int n, int requested)
     return m;
 }
 
-// Work items of the symmetric kernel for a device that owns virtual ranks [v0, v0 + nv): its row blocks ascending, and
-// for every chunk the number of items before it; chunk s pairs with the owned blocks that start below its end.
-static void sym_work_items(int n, const ChunkMap &cm, int v0, int nv, std::vector<int> *owned, std::vector<int> *prefix)
+// Work items of the symmetric kernel for a device that owns virtual ranks [v0, v0 + nv): every (owned row block,
+// chunk) pair whose chunk reaches above the block's first row, in dispatch order -- the long chunks row block by row
+// block (ascending), then the short chunks row block by row block.  Ascending row blocks put every item behind its
+// predecessor in the reaction-sum chain of its (virtual rank, segment) -- forces_sym.cuh waits on lower CTA indices
+// only -- and a row of items apart from it; the short items still come last and fill the tail of the launch.
+static void sym_work_items(int n, const ChunkMap &cm, int v0, int nv, std::vector<int2> *items)
 {
     const int nblocks = (n + SYM_RB - 1) / SYM_RB;
-    owned->clear();
-    for (int B = 0; B < nblocks; ++B) {
-        const int v = sym_vrank(B);
-        if (v >= v0 && v < v0 + nv) owned->push_back(B);
-    }
-    prefix->assign(static_cast<size_t>(cm.nsplit) + 1, 0);
-    size_t live = 0;
-    for (int s = 0; s < cm.nsplit; ++s) {
-        long long end = static_cast<long long>(chunk_start(cm, s)) + chunk_len(cm, s);
-        if (end > n) end = n;
-        while (live < owned->size() && static_cast<long long>((*owned)[live]) * SYM_RB < end) ++live;
-        (*prefix)[s + 1] = (*prefix)[s] + static_cast<int>(live);
+    items->clear();
+    for (int phase = 0; phase < 2; ++phase) {
+        const int s_lo = phase == 0 ? 0 : cm.nbig;
+        const int s_hi = phase == 0 ? cm.nbig : cm.nsplit;
+        for (int B = 0; B < nblocks; ++B) {
+            const int v = sym_vrank(B);
+            if (v < v0 || v >= v0 + nv) continue;
+            int s = chunk_of(cm, B * SYM_RB);   // the chunk that holds the block's first row
+            if (s < s_lo) s = s_lo;
+            for (; s < s_hi; ++s) items->push_back(make_int2(B, s));
+        }
     }
 }
 
 static int upload_sym_items(Shard &s, int n, const ChunkMap &cm, int v0, int nv)
 {
-    std::vector<int> owned, prefix;
-    sym_work_items(n, cm, v0, nv, &owned, &prefix);
-    if (s.cta_prefix) cudaFree(s.cta_prefix);
-    if (s.owned_sorted) cudaFree(s.owned_sorted);
-    s.cta_prefix = s.owned_sorted = nullptr;
-    NB_CUDA(cudaMalloc(&s.cta_prefix, sizeof(int) * prefix.size()));
-    NB_CUDA(cudaMalloc(&s.owned_sorted, sizeof(int) * (owned.empty() ? 1 : owned.size())));
-    NB_CUDA(cudaMemcpy(s.cta_prefix, prefix.data(), sizeof(int) * prefix.size(), cudaMemcpyHostToDevice));
-    if (!owned.empty()) NB_CUDA(cudaMemcpy(s.owned_sorted, owned.data(), sizeof(int) * owned.size(), cudaMemcpyHostToDevice));
-    s.sym_items = prefix.back();
+    std::vector<int2> items;
+    sym_work_items(n, cm, v0, nv, &items);
+    if (s.items) cudaFree(s.items);
+    s.items = nullptr;
+    NB_CUDA(cudaMalloc(&s.items, sizeof(int2) * (items.empty() ? 1 : items.size())));
+    if (!items.empty()) NB_CUDA(cudaMemcpy(s.items, items.data(), sizeof(int2) * items.size(), cudaMemcpyHostToDevice));
+    s.sym_items = static_cast<int>(items.size());
     return NBODY_GPU_OK;
 }
 
@@ -273,9 +273,10 @@ static void free_shard(Shard &s)
     if (s.arena) cudaFree(s.arena);
     if (s.mr) cudaFree(s.mr);
     if (s.part) cudaFree(s.part);
-    if (s.colpart) cudaFree(s.colpart);
-    if (s.cta_prefix) cudaFree(s.cta_prefix);
-    if (s.owned_sorted) cudaFree(s.owned_sorted);
+    if (s.vacc) cudaFree(s.vacc);
+    if (s.turn) cudaFree(s.turn);
+    if (s.sym_err) cudaFree(s.sym_err);
+    if (s.items) cudaFree(s.items);
     if (s.flush) cudaFree(s.flush);
     if (s.orig) cudaFree(s.orig);
     if (s.mr0) cudaFree(s.mr0);
@@ -291,7 +292,6 @@ static void free_shard(Shard &s)
     if (s.fscratch) cudaFree(s.fscratch);
     if (s.render_owner) cudaFree(s.render_owner);
     if (s.render_img) cudaFree(s.render_img);
-    if (s.p2p_err) cudaFree(s.p2p_err);
     for (cudaEvent_t e : s.prof_ev)
         if (e) cudaEventDestroy(e);
     if (s.ev0) cudaEventDestroy(s.ev0);
@@ -387,15 +387,17 @@ static int enqueue_forces(nbody_gpu *h, Shard &s, int slot, double2 *exact_out)
         a.pos = s.pos[slot];
         a.mr = s.mr;
         a.rowpart = s.part;
-        a.colpart = s.colpart;
+        a.vacc = s.vacc;
+        a.turn = s.turn;
+        a.nseg = s.nseg;
+        a.error_word = s.sym_err;
         a.boxes = s.boxes;
         a.n = h->n;
         a.npad = h->npad;
         a.cm = h->cm;
         a.v0 = s.v0;
         a.nv = s.nv;
-        a.cta_prefix = s.cta_prefix;
-        a.owned_sorted = s.owned_sorted;
+        a.items = s.items;
 #ifdef NBODY_DEV
         // development knob (read at init, see init_impl): the work items are those of ONE virtual rank only -- what
         // one GPU of an 8-way shard runs -- for timing and ncu on a single device; the step's results are garbage
@@ -420,7 +422,9 @@ static void enqueue_sym_reduce(nbody_gpu *h, Shard &s, bool to_peers)
 {
     SymReduceArgs a;
     a.rowpart = s.part;
-    a.colpart = s.colpart;
+    a.vacc = s.vacc;
+    a.turn = s.turn;
+    a.nseg = s.nseg;
     a.vbuf = s.vbuf;
     a.n = h->n;
     a.npad = h->npad;
@@ -676,9 +680,10 @@ static int sync_all(nbody_gpu *h)
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
         NB_CUDA(cudaStreamSynchronize(s.stream));
-        if (h->p2p && s.p2p_err) {
+        if (s.sym_err) {
             int e = 0;
-            NB_CUDA(cudaMemcpy(&e, s.p2p_err, sizeof e, cudaMemcpyDeviceToHost));
+            NB_CUDA(cudaMemcpy(&e, s.sym_err, sizeof e, cudaMemcpyDeviceToHost));
+            if (e == SYM_ERR_TURN) return fail(NBODY_GPU_ECUDA, "force kernel: a CTA gave up waiting for its turn to add reaction sums");
             if (e) return fail(NBODY_GPU_ECUDA, "peer exchange %c timed out waiting for another GPU", e == 1 ? 'A' : e == 2 ? 'B' : 'S');
         }
     }
@@ -786,8 +791,7 @@ static int setup_p2p(nbody_gpu *h)
     if (P > MAX_PEERS) return NBODY_GPU_OK;
     for (Shard &s : h->shards) {
         NB_CUDA(cudaSetDevice(s.device));
-        NB_CUDA(cudaMalloc(&s.p2p_err, sizeof(int)));
-        NB_CUDA(cudaMemsetAsync(s.p2p_err, 0, sizeof(int), s.stream));
+        s.p2p_err = s.sym_err;   // one error word per device (peer exchange implies the symmetric kernel)
         s.peers.epoch = s.epoch;
     }
     if (h->shards.size() > 1) {   // one process, several devices
@@ -1013,11 +1017,9 @@ int nbody_gpu_shard_plan(int n, int mode, int nranks, int rank, int out[8], long
         const ChunkMap cm = choose_split_sym(n, 0);
         const int nv = SYM_V / nranks, v0 = rank * nv;
         const int nblocks = (n + SYM_RB - 1) / SYM_RB;
-        const int slots = (nblocks + 2 * SYM_V - 1) / (2 * SYM_V) * 2 * nv;
         int owned = 0;
-        for (int k = 0; k < slots; ++k) {
-            const int B = sym_owned_block(k, v0, nv);
-            if (B >= nblocks) continue;
+        for (int B = 0; B < nblocks; ++B) {
+            if (sym_vrank(B) < v0 || sym_vrank(B) >= v0 + nv) continue;
             owned += 1;
             // the kernel's walk: directed pairs inside the block's own tiles, one evaluation per pair above it
             const long long rows = (B + 1) * SYM_RB <= n ? SYM_RB : n - B * SYM_RB;
@@ -1037,6 +1039,29 @@ int nbody_gpu_shard_plan(int n, int mode, int nranks, int rank, int out[8], long
         out[6] = nsplit;
     }
     if (pair_evaluations) *pair_evaluations = evals;
+    return NBODY_GPU_OK;
+}
+
+int nbody_gpu_sym_work_items(int n, int nranks, int rank, int *blocks, int *chunks, int cap, int *count,
+                             int *chunk_start_out, int chunk_cap, int *nchunks)
+{
+    if (n < 1 || nranks < 1 || rank < 0 || rank >= nranks || cap < 0 || !count) return fail(NBODY_GPU_EINVAL, "bad argument");
+    if (SYM_V % nranks != 0) return fail(NBODY_GPU_EINVAL, "the symmetric kernel shards over 1, 2, 4 or 8 GPUs");
+    const ChunkMap cm = choose_split_sym(n, 0);
+    const int nv = SYM_V / nranks;
+    std::vector<int2> items;
+    sym_work_items(n, cm, rank * nv, nv, &items);
+    *count = static_cast<int>(items.size());
+    for (int k = 0; k < *count && k < cap; ++k) {
+        if (blocks) blocks[k] = items[k].x;
+        if (chunks) chunks[k] = items[k].y;
+    }
+    if (nchunks) *nchunks = cm.nsplit;
+    if (chunk_start_out)
+        for (int s = 0; s <= cm.nsplit && s < chunk_cap; ++s) {
+            long long at = s < cm.nsplit ? chunk_start(cm, s) : n;
+            chunk_start_out[s] = static_cast<int>(at < n ? at : n);
+        }
     return NBODY_GPU_OK;
 }
 
@@ -1119,9 +1144,9 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
     const size_t bytes = sizeof(double2) * static_cast<size_t>(h->npad);
     if (h->symmetric) {
         h->cm = choose_split_sym(h->n, cfg->jsplit);
-        // the reaction partial sums grow with n^2: when they do not fit the device, the directed
-        // kernel (2x the pair evaluations, O(n) memory) runs instead
-        const size_t slots = static_cast<size_t>((h->nblocks + 2 * SYM_V - 1) / (2 * SYM_V)) * 2 * (SYM_V / P);
+        // the row-side partial sums grow with n * nsplit: when they do not fit the device, the
+        // directed kernel (2x the pair evaluations, fewer chunks) runs instead
+        const size_t slots = static_cast<size_t>(SYM_V / P);
         size_t free_b = 0, total_b = 0;
         if (multi_dev) NB_CUDA(cudaSetDevice(0));
         else if (cfg->device >= 0) NB_CUDA(cudaSetDevice(cfg->device));
@@ -1177,12 +1202,13 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
             if (h->symmetric) {
                 s.nv = SYM_V / P;
                 s.v0 = s.part_index * s.nv;
-                // colpart slots = grid.x of the force kernel: whole groups of 2*SYM_V row blocks; slots whose
-                // block lies beyond the last body exit at once
-                const size_t slots = static_cast<size_t>((h->nblocks + 2 * SYM_V - 1) / (2 * SYM_V)) * 2 * s.nv;
-                s.nblocks_owned = static_cast<int>(slots);
-                NB_CUDA(cudaMalloc(&s.colpart, bytes * slots));
-                NB_CUDA(cudaMemsetAsync(s.colpart, 0, bytes * slots, s.stream));
+                s.nseg = seg_count(h->cm);
+                NB_CUDA(cudaMalloc(&s.vacc, bytes * s.nv));
+                NB_CUDA(cudaMemsetAsync(s.vacc, 0, bytes * s.nv, s.stream));
+                NB_CUDA(cudaMalloc(&s.turn, sizeof(int) * static_cast<size_t>(s.nv) * s.nseg));
+                NB_CUDA(cudaMemsetAsync(s.turn, 0, sizeof(int) * static_cast<size_t>(s.nv) * s.nseg, s.stream));
+                NB_CUDA(cudaMalloc(&s.sym_err, sizeof(int)));
+                NB_CUDA(cudaMemsetAsync(s.sym_err, 0, sizeof(int), s.stream));
                 int items_v0 = s.v0, items_nv = s.nv;
 #ifdef NBODY_DEV
                 if (const char *e = getenv("NBODY_DEV_VRANK")) {
@@ -1595,13 +1621,18 @@ int nbody_gpu_describe(const nbody_gpu *h, char *buf, int len)
                               "{\"mode\": \"%s\", \"kernel\": \"%s\", \"symmetric\": %s, \"nsplit\": %d, \"chunk\": %d, "
                               "\"short_chunks\": %d, \"row_blocks\": %d, \"shards\": %d, \"graph_steps\": %d, \"single_launch_loop\": %s, "
                               "\"exchange\": \"%s\", \"fp64_instr_per_pair\": %.1f, "
-                              "\"cell_order\": %s, \"fused_tile_boxes\": %s, \"sort_interval\": %d, \"sorts\": %lld}",
+                              "\"cell_order\": %s, \"fused_tile_boxes\": %s, \"sort_interval\": %d, \"sorts\": %lld, "
+                              "\"partial_sum_bytes\": %lld}",
                               fast ? "fast" : "exact", kernel, h->symmetric ? "true" : "false", h->nsplit,
                               h->symmetric ? h->cm.chunk : h->chunk, h->symmetric ? h->cm.nsplit - h->cm.nbig : 0,
                               h->symmetric ? h->nblocks : 0, h->nshards_total, graph, h->small ? "true" : "false",
                               !h->sharded ? "none" : h->p2p ? "peer-memory stores + barrier kernels" : "ncclAllGather", ipp,
                               h->sorted ? "true" : "false", h->fused_boxes ? "true" : "false",
-                              h->sorted ? h->sort_interval : 0, h->sorts);
+                              h->sorted ? h->sort_interval : 0, h->sorts,
+                              // device memory of the fast kernels' partial sums, per GPU: row sums per j-chunk, and the
+                              // symmetric kernel's reaction sums per owned virtual rank
+                              !fast ? 0LL : static_cast<long long>(sizeof(double2)) * h->npad *
+                                  (h->nsplit + (h->symmetric ? h->shards[0].nv : 0)));
     if (buf && len > 0) {
         strncpy(buf, tmp, static_cast<size_t>(len) - 1);
         buf[len - 1] = 0;

@@ -67,18 +67,8 @@ __global__ void __launch_bounds__(128) sym_reduce_p2p_kernel(const SymReduceArgs
     if (j >= a.n) return;
     const int v = a.v0 + blockIdx.y;
     const int blk = j / SYM_RB;
-    double xf = 0.0, yf = 0.0;
-    for (int g0 = 0; g0 < blk; g0 += 2 * SYM_V) {
-        const int Bs[2] = {g0 + v, g0 + 2 * SYM_V - 1 - v};
-#pragma unroll
-        for (int q = 0; q < 2; ++q) {
-            if (Bs[q] < blk) {
-                const double2 c = a.colpart[static_cast<size_t>(sym_local_block(Bs[q], a.v0, a.nv)) * a.npad + j];
-                xf += c.x;
-                yf += c.y;
-            }
-        }
-    }
+    const double2 r = sym_take_reactions(a, j, blockIdx.y);
+    double xf = r.x, yf = r.y;
     if (sym_vrank(blk) == v) {
         for (int s = chunk_of(a.cm, blk * SYM_RB); s < a.cm.nsplit; ++s) {
             const double2 c = a.rowpart[static_cast<size_t>(s) * a.npad + j];

@@ -49,22 +49,36 @@ __host__ __device__ inline int chunk_of(const ChunkMap &m, int j)
     return j < m.jsmall0 ? j / m.chunk : m.nbig + (j - m.jsmall0) / m.csmall;
 }
 
+// Reaction sums are handed from CTA to CTA in segments of SYM_SEG bodies j: a long chunk holds segs_per_chunk()
+// of them, a short chunk is one.
+constexpr int SYM_SEG = 1024;
+__host__ __device__ inline int segs_per_chunk(const ChunkMap &m) { return (m.chunk + SYM_SEG - 1) / SYM_SEG; }
+__host__ __device__ inline int seg_count(const ChunkMap &m) { return m.nbig * segs_per_chunk(m) + (m.nsplit - m.nbig); }
+
 struct SymArgs {
     const double2 *pos;
     const double2 *mr;
     double2 *rowpart;     // [nsplit][npad]  row-side partial sums
-    double2 *colpart;     // [nblocks][npad] reaction (column-side) partial sums, valid for j >= (B+1)*SYM_RB
+    // Reaction (column-side) sums: vacc[v - v0][j] collects, for virtual rank v, the reactions on body j from v's
+    // row blocks below block(j), B ascending.  The CTAs of one (v, segment) chain add their share one after the
+    // other: turn[(v - v0) * nseg + seg] counts the blocks that have added theirs (forces_sym.cuh).  Both are zero
+    // at launch (sym_reduce_kernel leaves them so).
+    double2 *vacc;        // [nv][npad]
+    int *turn;            // [nv][nseg]
+    int nseg;
+    int *error_word;      // set to SYM_ERR_TURN when a CTA gave up waiting for its turn
     const double *boxes;  // [ceil(n/TILE_J)][8] per-tile bounding boxes (xmin ymin xmax ymax rmax . . .), or nullptr
     int n;
     int npad;
     ChunkMap cm;
-    int v0, nv;           // this device owns the row blocks B with (B % SYM_V) in [v0, v0+nv): "virtual ranks"
-    // The grid holds live work items only: item c = (chunk s, owned block), chunk-major.  cta_prefix[s] = items before
-    // chunk s (nsplit + 1 entries), owned_sorted = this device's row blocks ascending; chunk s pairs with the first
-    // cta_prefix[s+1] - cta_prefix[s] of them (the blocks that start below the chunk's end).
-    const int *cta_prefix;
-    const int *owned_sorted;
+    int v0, nv;           // this device owns the row blocks B with sym_vrank(B) in [v0, v0+nv): "virtual ranks"
+    // The grid holds live work items only, one CTA per item (x = row block, y = chunk), in dispatch order: row block
+    // by row block (ascending) over the long chunks, then row block by row block over the short chunks -- the
+    // predecessor of an item in its (v, segment) chain is at least a row of items ahead of it, and the short items
+    // still fill the tail of the launch.
+    const int2 *items;
 };
+constexpr int SYM_ERR_TURN = 16;
 
 // The symmetric kernel's partial sums are combined through SYM_V fixed "virtual ranks": row block B
 // belongs to virtual rank sym_vrank(B); vbuf[v][j] = reactions on j from v's blocks below block(j)
@@ -81,22 +95,16 @@ __host__ __device__ inline int sym_vrank(int B)
     const int r = B % (2 * SYM_V);
     return r < SYM_V ? r : 2 * SYM_V - 1 - r;
 }
-// local slot of row block B in a device's colpart array (device owns virtual ranks [v0, v0+nv))
-__host__ __device__ inline int sym_local_block(int B, int v0, int nv)
+// position of row block B among the blocks of its virtual rank, ascending (16g+v, 16g+15-v, 16(g+1)+v, ...)
+__host__ __device__ inline int sym_vrank_seq(int B)
 {
-    const int r = B % (2 * SYM_V);
-    const int half = r < SYM_V ? 0 : 1;
-    return (B / (2 * SYM_V)) * 2 * nv + half * nv + (sym_vrank(B) - v0);
-}
-// inverse: k-th owned block (ascending B within each virtual rank)
-__host__ __device__ inline int sym_owned_block(int k, int v0, int nv)
-{
-    const int g = k / (2 * nv), r = k % (2 * nv);
-    return r < nv ? g * 2 * SYM_V + v0 + r : g * 2 * SYM_V + 2 * SYM_V - 1 - (v0 + r - nv);
+    return 2 * (B / (2 * SYM_V)) + ((B % (2 * SYM_V)) < SYM_V ? 0 : 1);
 }
 struct SymReduceArgs {
     const double2 *rowpart;
-    const double2 *colpart;
+    double2 *vacc;        // [nv][npad] reaction sums of the force kernel; read, then zeroed for the next launch
+    int *turn;            // [nv][nseg] zeroed for the next launch
+    int nseg;
     double2 *vbuf;        // [SYM_V][npad]
     int n, npad;
     ChunkMap cm;

@@ -391,3 +391,36 @@ def test_pinned_host_buffers_round_trip(nb, oracle):
         g.sync()
         for a in host:
             nb.unpin_host(a)
+
+
+@pytest.mark.parametrize("jsplit", [0, 1, 5])
+def test_reaction_sums_handed_from_cta_to_cta(nb, oracle, jsplit):
+    """The symmetric kernel adds a row block's reaction sums to vacc[v][j] when it is that block's turn in the chain
+    of its (virtual rank, 1024-body segment) -- forces_sym.cuh.  Ragged N (last segment, tile and row block are
+    partial), chunk shapes with one segment per CTA (jsplit = 0: 1024-body chunks + one-tile chunks) and with many
+    (jsplit = 1: one chunk of 41 segments; 5: 9 segments each): forces of block-boundary and random bodies against
+    the oracle's row form (nbody-seq.c:87-107), and -- the order of the additions being fixed -- the same bits from
+    a second launch on the same handle (the counts and sums are left clean), after steps, and from a second handle."""
+    n = 40000 + 37
+    b = oracle.init_bodies(n)
+    b.x[n - 1], b.y[n - 1] = b.x[5], b.y[5]           # a coincident pair across the whole index range
+    g = make(nb, b, mode=nb.MODE_FAST, jsplit=jsplit)
+    d = g.describe()
+    assert d["symmetric"] and d["cell_order"], d
+    order = oracle.cell_order(nb, b.x, b.y)
+    rows = np.unique(np.concatenate([oracle.block_sample(order, per_block_extra=1), [0, 5, n - 1]])).astype(np.int32)
+    wxf, wyf = oracle.forces_for(rows, b.x, b.y, b.mass, b.radius)
+    fx, fy = g.forces()
+    full_x, full_y = oracle.forces_for(np.arange(0, n, 53, dtype=np.int32), b.x, b.y, b.mass, b.radius)
+    fmax = max(np.abs(wxf).max(), np.abs(wyf).max(), np.abs(full_x).max(), np.abs(full_y).max())
+    assert np.abs(fx[rows] - wxf).max() <= FRC_RTOL_OF_MAX * fmax and np.abs(fy[rows] - wyf).max() <= FRC_RTOL_OF_MAX * fmax
+    assert np.abs(fx[::53] - full_x).max() <= FRC_RTOL_OF_MAX * fmax and np.abs(fy[::53] - full_y).max() <= FRC_RTOL_OF_MAX * fmax
+    fx2, fy2 = g.forces()
+    assert np.array_equal(fx.view(np.uint64), fx2.view(np.uint64)) and np.array_equal(fy.view(np.uint64), fy2.view(np.uint64))
+    g.step(3)
+    h = make(nb, b, mode=nb.MODE_FAST, jsplit=jsplit)
+    h.step(1)
+    h.step(2)
+    for a, c in zip(g.fetch(), h.fetch()):
+        assert np.array_equal(a.view(np.uint64), c.view(np.uint64))
+    assert abs(fx.sum()) <= 1e-6 * np.abs(fx).sum() and abs(fy.sum()) <= 1e-6 * np.abs(fy).sum()   # Newton's third law
