@@ -423,19 +423,17 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
                 int *turn = a.turn + static_cast<size_t>(vloc) * a.nseg + seg0 + segi;
                 if (tid == 0) turn_wait(turn, seq, a.error_word);
                 __syncthreads();
-                double2 *acc = a.vacc + static_cast<size_t>(vloc) * a.npad;
+                // the additions are done by the L2 (RED.ADD.F64, nothing comes back to the SM): one IEEE add per
+                // element like a load/add/store would do, and -- it being this block's turn -- nobody else touches
+                // these elements until the fence below has seen them complete
+                double *acc = reinterpret_cast<double *>(a.vacc + static_cast<size_t>(vloc) * a.npad);
                 for (int j = lo + tid; j < send; j += SYM_THREADS) {
-                    double2 t = __ldcg(acc + j);   // L2: the line may sit stale in this SM's L1 from an earlier CTA
                     const double2 c = s_seg[j - sstart];
-                    t.x += c.x;
-                    t.y += c.y;
-                    __stcg(acc + j, t);
+                    atomicAdd(acc + 2 * j, c.x);
+                    atomicAdd(acc + 2 * j + 1, c.y);
                 }
                 __syncthreads();
-                if (tid == 0) {
-                    __threadfence();
-                    turn_pass(turn, seq + 1);
-                }
+                if (tid == 0) turn_pass(turn, seq + 1);   // release at GPU scope, cumulative over the barrier above
             }
         }
     }

@@ -28,7 +28,7 @@ void launch_integrate_fast(const IntegrateArgs &a, cudaStream_t st)
 
 // Two shapes of the symmetric kernel, chosen by n alone (like every other choice that fixes the summation
 // order): 64 threads x 8 bodies (2 warps per CTA; one LDS pair, one accumulator rotation and one address update
-// serve 8 pairs) from SYM_WIDE_N bodies on, 128 x 4 below (more, shorter CTAs: better tail at N = 65536).
+// serve 8 pairs) from SYM_WIDE_N bodies on, 128 x 4 below (more, shorter CTAs: better tail when the launch has few).
 // NBODY_DEV builds can pin either shape with NBODY_SYM_VARIANT=1|2 for A/B timing.
 int launch_forces_sym(const SymArgs &a, int nitems, cudaStream_t st)
 {

@@ -207,19 +207,27 @@ static ChunkMap choose_split_sym(int n, int requested)
 
 // Work items of the symmetric kernel for a device that owns virtual ranks [v0, v0 + nv): every (owned row block,
 // chunk) pair whose chunk reaches above the block's first row, in dispatch order -- the long chunks row block by row
-// block (ascending), then the short chunks row block by row block.  Ascending row blocks put every item behind its
-// predecessor in the reaction-sum chain of its (virtual rank, segment) -- forces_sym.cuh waits on lower CTA indices
-// only -- and a row of items apart from it; the short items still come last and fill the tail of the launch.
+// block, then the short chunks row block by row block.  The row blocks of a group of 2*SYM_V go in the order
+// 16g+v (v = v0, v0+1, ...) then 16g+15-v (v = v0, v0+1, ...): every virtual rank's blocks still ascend, which
+// puts every item behind its predecessor in the reaction-sum chain of its (virtual rank, segment) -- forces_sym.cuh
+// waits on lower CTA indices only -- and the two are nv rows of items apart (8 rows on one GPU: the predecessor
+// finished long ago; one row on an 8-way shard: it started about half a CTA lifetime earlier).  The short items
+// still come last and fill the tail of the launch.
 static void sym_work_items(int n, const ChunkMap &cm, int v0, int nv, std::vector<int2> *items)
 {
     const int nblocks = (n + SYM_RB - 1) / SYM_RB;
+    std::vector<int> rows;
+    for (int g0 = 0; g0 < nblocks; g0 += 2 * SYM_V)
+        for (int half = 0; half < 2; ++half)
+            for (int v = v0; v < v0 + nv; ++v) {
+                const int B = half == 0 ? g0 + v : g0 + 2 * SYM_V - 1 - v;
+                if (B < nblocks) rows.push_back(B);
+            }
     items->clear();
     for (int phase = 0; phase < 2; ++phase) {
         const int s_lo = phase == 0 ? 0 : cm.nbig;
         const int s_hi = phase == 0 ? cm.nbig : cm.nsplit;
-        for (int B = 0; B < nblocks; ++B) {
-            const int v = sym_vrank(B);
-            if (v < v0 || v >= v0 + nv) continue;
+        for (int B : rows) {
             int s = chunk_of(cm, B * SYM_RB);   // the chunk that holds the block's first row
             if (s < s_lo) s = s_lo;
             for (; s < s_hi; ++s) items->push_back(make_int2(B, s));

@@ -23,7 +23,7 @@ struct ForceArgs {
 };
 
 constexpr int SYM_RB = 512;         // rows per block of the symmetric (evaluate-each-pair-once) kernel
-constexpr int SYM_WIDE_N = 131072;  // from this many bodies on: 64 threads x 8 bodies per CTA instead of 128 x 4
+constexpr int SYM_WIDE_N = 49152;   // from this many bodies on: 64 threads x 8 bodies per CTA instead of 128 x 4 (profiles/r2_shape_sweep.log)
 constexpr int SYM_BOX_DOUBLES = 8;  // per-tile bounding box: xmin ymin xmax ymax rmax + padding (one 64-byte bulk copy)
 
 // j-chunks of the symmetric kernel: `nbig` chunks of `chunk` bodies cover [0, jsmall0), then chunks of `csmall`

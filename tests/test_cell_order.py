@@ -175,7 +175,7 @@ def test_cell_order_same_bits_on_1_2_4_8_gpus(nb, oracle):
 
 
 def test_wide_kernel_same_bits_across_gpu_counts(nb, oracle):
-    """N >= 131072 runs the 64 x 8 shape of the symmetric kernel (2 warps per CTA, 8 bodies per thread) with
+    """N >= 49152 runs the 64 x 8 shape of the symmetric kernel (2 warps per CTA, 8 bodies per thread) with
     max(1024, N/256)-body j-chunks: still a function of N only, so 1, 2, 4 and 8 GPUs give the same bits; and the
     result stays within tolerance of the directed kernel (an independent summation structure)."""
     n, steps = 131072 + 300, 2

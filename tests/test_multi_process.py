@@ -51,7 +51,7 @@ def test_symmetric_fast_sharded_processes_same_bits_as_one_gpu(nb, p2p):
 
 
 def test_wide_kernel_sharded_processes_same_bits_as_one_gpu(nb):
-    """N >= 131072: the 64 x 8 shape with short tail chunks, the configuration the headline number is made of."""
+    """N >= 49152: the 64 x 8 shape with short tail chunks, the configuration the headline number is made of."""
     for world in _worlds(nb):
         out = _launch(world, "--bodies", 131072 + 300, "--mode", 1, "--k1", 2, "--k2", 2)
         assert out["bits_equal_to_1gpu_on_every_rank"] is True, out

@@ -13,4 +13,4 @@ ncu --set full --clock-control none --import-source on -k regex:forces_sym -s 4 
 NBODY_GPU_LIB=$DEVLIB NBODY_DEV_VRANK=3 python tools/vrank_times.py one 262144 > gpurun_out/r2_plain_8way.json 2> gpurun_out/r2_plain_8way.err || { echo "plain 8way failed"; exit 1; }
 NBODY_GPU_LIB=$DEVLIB NBODY_DEV_VRANK=3 ncu --set full --clock-control none --import-source on -k regex:forces_sym -s 3 -c 1 -f -o gpurun_out/r2_prof_8way python tools/vrank_times.py one 262144 > gpurun_out/r2_ncu_full_8way.log 2>&1
 ls -la gpurun_out/*.ncu-rep
-tail -3 gpurun_out/r2_ncu_full_c4.log gpurun_out/r2_ncu_full_c3.log gpurun_out/r2_ncu_full_8way.log
+tail -n 3 gpurun_out/r2_ncu_full_c4.log gpurun_out/r2_ncu_full_c3.log gpurun_out/r2_ncu_full_8way.log
