@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define NBODY_GPU_ABI_VERSION 3
+#define NBODY_GPU_ABI_VERSION 4
 
 enum {
     NBODY_GPU_OK = 0,
@@ -184,12 +184,18 @@ int nbody_gpu_shard_plan(int n, int mode, int nranks, int rank, int out[8], long
 /* The symmetric kernel's work items for rank `rank` of `nranks` (host arithmetic only; the library's own table):
  * item k is CTA k of the force kernel = (row block blocks[k], j-chunk chunks[k]), in dispatch order.  Writes at most
  * `cap` items, *count = the number there are.  Chunk s covers bodies [chunk_start[s], chunk_start[s+1]) --
- * chunk_start (may be NULL) receives at most chunk_cap entries, *nchunks = the number of chunks.  The reaction sums
- * of one (virtual rank, 1024-body segment) are added by that virtual rank's row blocks in ascending order, each
- * CTA waiting for the previous one: tests check that the CTA waited for always has a lower index (it is dispatched
- * earlier, so the wait cannot deadlock).  Returns NBODY_GPU_EINVAL when the symmetric kernel would not be used. */
-int nbody_gpu_sym_work_items(int n, int nranks, int rank, int *blocks, int *chunks, int cap, int *count,
-                             int *chunk_start, int chunk_cap, int *nchunks);
+ * chunk_start (may be NULL) receives at most chunk_cap entries, *nchunks = the number of chunks.
+ * Two hand-overs between CTAs fix the order of the sums, and tests check from this table that every CTA waited for
+ * has a lower index (it is dispatched earlier, so no wait can deadlock):
+ *  - the reaction sums of one (virtual rank, 1024-body segment) are added by that virtual rank's row blocks in
+ *    ascending order, each CTA waiting for the previous one;
+ *  - the row sums of a group groups[k] (a row block's long-chunk items, or its short-chunk items: consecutive items)
+ *    are left in a ring of *ring slices (slot = k % ring) by all items but the group's last, which adds them in
+ *    chunk order; guards[k] = the group whose fold must be over before item k may overwrite its slot (-1: none).
+ * Any of blocks/chunks/groups/guards/ring may be NULL.  Returns NBODY_GPU_EINVAL when the symmetric kernel would
+ * not be used. */
+int nbody_gpu_sym_work_items(int n, int nranks, int rank, int *blocks, int *chunks, int *groups, int *guards, int cap,
+                             int *count, int *chunk_start, int chunk_cap, int *nchunks, int *ring);
 
 /* The reference's own partition rule, for comparison (nbody-par.c:225-263):
  * counts n/P, ranks 1..n%P get one more; displacements are the prefix sum. */

@@ -89,7 +89,7 @@ def lib():
     L.nbody_gpu_shard_plan.argtypes = [ci, ci, ci, ci, ctypes.POINTER(ci), ctypes.POINTER(ctypes.c_longlong)]
     ip = ctypes.POINTER(ci)
     if not os.environ.get("NBODY_GPU_LIB") or hasattr(L, "nbody_gpu_sym_work_items"):   # an older build under A/B test may lack it
-        L.nbody_gpu_sym_work_items.argtypes = [ci, ci, ci, ip, ip, ci, ip, ip, ci, ip]
+        L.nbody_gpu_sym_work_items.argtypes = [ci, ci, ci, ip, ip, ip, ip, ci, ip, ip, ci, ip, ip]
     L.nbody_gpu_pin_host.argtypes = [vp, ctypes.c_size_t]
     L.nbody_gpu_unpin_host.argtypes = [vp]
     _lib = L
@@ -134,17 +134,22 @@ def shard_plan(n, mode, nranks, rank):
 
 
 def sym_work_items(n, nranks=1, rank=0):
-    """The symmetric kernel's (row block, chunk) work items of one rank in dispatch order, and the chunk boundaries:
-    (blocks, chunks, chunk_start) as int32 arrays (chunk s covers bodies chunk_start[s]..chunk_start[s+1])."""
-    count, nchunks = ctypes.c_int(), ctypes.c_int()
-    _check(lib().nbody_gpu_sym_work_items(n, nranks, rank, None, None, 0, ctypes.byref(count), None, 0, ctypes.byref(nchunks)))
-    blocks = np.empty(count.value, dtype=np.int32)
-    chunks = np.empty(count.value, dtype=np.int32)
+    """The symmetric kernel's work items of one rank in dispatch order: dict of int32 arrays `blocks`, `chunks`, `groups`,
+    `guards` (one entry per item = CTA), `chunk_start` (chunk s covers bodies chunk_start[s]..chunk_start[s+1]) and
+    the length `ring` of the row-sum slice ring."""
+    count, nchunks, ring = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    _check(lib().nbody_gpu_sym_work_items(n, nranks, rank, None, None, None, None, 0, ctypes.byref(count), None, 0,
+                                          ctypes.byref(nchunks), ctypes.byref(ring)))
+    cols = {k: np.empty(count.value, dtype=np.int32) for k in ("blocks", "chunks", "groups", "guards")}
     start = np.empty(nchunks.value + 1, dtype=np.int32)
     ip = ctypes.POINTER(ctypes.c_int)
-    _check(lib().nbody_gpu_sym_work_items(n, nranks, rank, blocks.ctypes.data_as(ip), chunks.ctypes.data_as(ip), count.value,
-                                          ctypes.byref(count), start.ctypes.data_as(ip), nchunks.value + 1, ctypes.byref(nchunks)))
-    return blocks, chunks, start
+    _check(lib().nbody_gpu_sym_work_items(n, nranks, rank, cols["blocks"].ctypes.data_as(ip), cols["chunks"].ctypes.data_as(ip),
+                                          cols["groups"].ctypes.data_as(ip), cols["guards"].ctypes.data_as(ip), count.value,
+                                          ctypes.byref(count), start.ctypes.data_as(ip), nchunks.value + 1,
+                                          ctypes.byref(nchunks), ctypes.byref(ring)))
+    cols["chunk_start"] = start
+    cols["ring"] = ring.value
+    return cols
 
 
 def reference_init(n, xdim=1024, ydim=768):

@@ -16,15 +16,19 @@
 //     fixed, the result is deterministic, and the reaction sums take nv * N * 16 B instead
 //     of one N-vector per row block.  CTAs are dispatched row block by row block, so the
 //     CTA a turn waits for started a row of CTAs earlier and has normally long finished.
-// Far field: with the bodies in cell order (sort_kernels.cuh) most (row block, j tile) pairs are further apart
+// Far field: with the bodies in cell order (kernels_sort.cu) most (row block, j tile) pairs are further apart
 // than any r_i + r_j of their bodies.  Every tile carries a bounding box (x/y range, largest radius; one more
 // TMA copy per tile); if the gap between the block's box and the tile's box is at least rmax_B + rmax_T the
 // clamp max(dsqr, mindsqr) is the identity for every pair of the tile and no two bodies can coincide, so the
-// tile runs the far-field form of the pair: 17 FP64-pipe instructions and no integer work.  The test uses the
+// tile runs the far-field form of the pair: 16 FP64-pipe instructions and no integer work.  The test uses the
 // same rounded operations as the pair itself (monotone), so it is exact and both forms give the same bits.
-// sym_reduce_kernel then adds each body's row sums to its block's virtual rank: SYM_V per-virtual-rank vectors (step_args.h), and
-// integrate_kernel adds those in a fixed order: the same bits on 1, 2, 4 or 8 GPUs.  Per unordered pair: 19 FP64-pipe instructions (13 shared, 3 per side)
-// + 1 MUFU + ~8 ALU/LSU + 0.3 SHFL, against 2 x (16 + ...) for the directed kernel.
+// Row sums: the CTAs of one row block leave their sums in a ring of slices and count themselves in; the block's last
+// CTA in dispatch order waits for the count and adds the slices in chunk order (rowsum[phase][i]; a small ring that
+// stays in the L2 instead of one N-vector per j-chunk in HBM).
+// sym_reduce_kernel then adds each body's row sums to its block's virtual rank: SYM_V per-virtual-rank vectors
+// (step_args.h), and integrate_kernel adds those in a fixed order: the same bits on 1, 2, 4 or 8 GPUs.
+// Per unordered pair: 18 FP64-pipe instructions (16 in far-field tiles) + 1 MUFU + 1.5 .. 6 ALU/LSU/SHFL, against
+// 2 x (16 + ...) for the directed kernel.
 #pragma once
 #include <cuda_runtime.h>
 #include <cstdint>
@@ -201,6 +205,17 @@ __device__ __forceinline__ void turn_pass(int *turn, int next)
 {
     asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(turn), "r"(next) : "memory");
 }
+// count this CTA into its group (release: its slice is visible first): a reduction, nothing comes back
+__device__ __forceinline__ void group_arrive(int *cnt)
+{
+    asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(cnt) : "memory");
+}
+__device__ __forceinline__ int peek_acquire(const int *p)
+{
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 
 // Rare path, row side of a tile above the block (all j > i): + m_j / mindsqr for coincident j.
 __device__ __noinline__ double sym_row_rescan(const double2 *s_pos, const double2 *s_mr, int cnt, double xi, double yi,
@@ -247,14 +262,14 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     double *s_box = reinterpret_cast<double *>(s_seg + SYM_SEG);              // [STAGES][SYM_BOX_DOUBLES] tile boxes
     double *s_bbox = s_box + STAGES * SYM_BOX_DOUBLES;                        // [SYM_BOX_DOUBLES] this row block's box
     uint64_t *s_full = reinterpret_cast<uint64_t *>(s_bbox + SYM_BOX_DOUBLES);
-    int *s_flag = reinterpret_cast<int *>(s_full + STAGES);                 // [2] coincidence flags
+    int *s_flag = reinterpret_cast<int *>(s_full + STAGES);                 // [2] coincidence flags, [1] ring slot free
 
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int warp = tid >> 5;
     // grid = the live (row block, chunk) items in dispatch order (SymArgs::items): no CTA is launched for a chunk that
     // lies entirely below its row block
-    const int2 item = a.items[blockIdx.x];
+    const int4 item = a.items[blockIdx.x];
     const int blk = item.x;   // row block index
     const int by = item.y;    // chunk index
     const int i0 = blk * SYM_RB;
@@ -274,6 +289,9 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
         mbar_init_fence();
         s_flag[0] = 0;
         s_flag[1] = 0;
+        // the ring slot this item will leave its row sums in: the fold that read its previous contents is a ring of
+        // CTAs back -- look now, behind the prologue's latencies, and wait at the end only if it is not over yet
+        s_flag[2] = item.w < 0 || peek_acquire(a.gdone + item.w) == 1;
     }
     if (tid == 32 && a.boxes) {
         // bounding box of this row block = union of its tiles' boxes
@@ -438,11 +456,51 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
         }
     }
 
+    // Row sums.  Every item of the group but the last leaves its SYM_RB sums in its ring slice and counts itself
+    // in; the last item (in dispatch order: the others have lower CTA indices, they are running or done) waits for
+    // the count, adds the slices in chunk order, its own sums last, and writes the block's rows of rowsum[phase].
+    {
+        const int2 grp = a.groups[item.z];   // (first item, items)
+        const bool folds = static_cast<int>(blockIdx.x) == grp.x + grp.y - 1;
+        if (!folds) {
+            if (!s_flag[2]) {   // block-uniform; normally the slot was free when the CTA started
+                if (tid == 0) turn_wait(a.gdone + item.w, 1, a.error_word);
+                __syncthreads();
+            }
+            double2 *slice = a.slices + static_cast<size_t>(blockIdx.x % SYM_RING) * SYM_RB;
 #pragma unroll
-    for (int k = 0; k < SYM_IB; ++k) {
-        if (idx[k] < a.n) {
-            const double gm = NBODY_SYM_G * b[k].m;
-            a.rowpart[static_cast<size_t>(by) * a.npad + idx[k]] = make_double2(gm * b[k].ax, gm * b[k].ay);
+            for (int k = 0; k < SYM_IB; ++k) {
+                const double gm = NBODY_SYM_G * b[k].m;
+                __stcg(slice + (idx[k] - i0), make_double2(gm * b[k].ax, gm * b[k].ay));
+            }
+            __syncthreads();
+            if (tid == 0) group_arrive(a.gcnt + item.z);
+        } else {
+            if (tid == 0) turn_wait(a.gcnt + item.z, grp.y - 1, a.error_word);
+            __syncthreads();
+            double sx[SYM_IB], sy[SYM_IB];
+#pragma unroll
+            for (int k = 0; k < SYM_IB; ++k) sx[k] = sy[k] = 0.0;
+#pragma unroll 2
+            for (int t = 0; t < grp.y - 1; ++t) {
+                const double2 *slice = a.slices + static_cast<size_t>((grp.x + t) % SYM_RING) * SYM_RB + tid;
+#pragma unroll
+                for (int k = 0; k < SYM_IB; ++k) {
+                    const double2 c = __ldcg(slice + k * SYM_THREADS);
+                    sx[k] += c.x;
+                    sy[k] += c.y;
+                }
+            }
+            double2 *out = a.rowsum + (by < a.cm.nbig ? 0 : static_cast<size_t>(a.npad));
+#pragma unroll
+            for (int k = 0; k < SYM_IB; ++k) {
+                if (idx[k] < a.n) {
+                    const double gm = NBODY_SYM_G * b[k].m;
+                    out[idx[k]] = make_double2(sx[k] + gm * b[k].ax, sy[k] + gm * b[k].ay);
+                }
+            }
+            __syncthreads();
+            if (tid == 0) turn_pass(a.gdone + item.z, 1);
         }
     }
 }
@@ -455,6 +513,11 @@ __device__ __forceinline__ double2 sym_take_reactions(const SymReduceArgs &a, in
     const double2 r = *p;
     *p = make_double2(0.0, 0.0);
     if (j < a.nseg) a.turn[static_cast<size_t>(vl) * a.nseg + j] = 0;
+    if (vl == 0)
+        for (int q = j; q < a.ngroups; q += a.n) {
+            a.gcnt[q] = 0;
+            a.gdone[q] = 0;
+        }
     return r;
 }
 
@@ -467,9 +530,10 @@ __global__ void __launch_bounds__(128) sym_reduce_kernel(const SymReduceArgs a)
     const int blk = j / SYM_RB;
     const double2 r = sym_take_reactions(a, j, blockIdx.y);   // v's blocks below block(j), B ascending
     double xf = r.x, yf = r.y;
-    if (sym_vrank(blk) == v) {                // j's own row sums, chunk ascending
-        for (int s = chunk_of(a.cm, blk * SYM_RB); s < a.cm.nsplit; ++s) {
-            const double2 t = a.rowpart[static_cast<size_t>(s) * a.npad + j];
+    if (sym_vrank(blk) == v) {                // j's own row sums: over the long chunks, then over the short ones
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            const double2 t = a.rowsum[static_cast<size_t>(p) * a.npad + j];
             xf += t.x;
             yf += t.y;
         }

@@ -105,8 +105,14 @@ struct Shard {
     PeerTable peers = {};        // fused peer-memory exchange (npeers = 0: not in use)
     int *p2p_err = nullptr;      // = sym_err: ... or a barrier kernel timed out (1 + phase)
     std::vector<void *> ipc_opened;
-    int2 *items = nullptr;       // symmetric kernel: (row block, chunk) work items in dispatch order (SymArgs)
+    int4 *items = nullptr;       // symmetric kernel: (row block, chunk, group, guard) work items in dispatch order (SymArgs)
     int sym_items = 0;           // symmetric kernel: grid size
+    int2 *groups = nullptr;      // symmetric kernel: (first item, items) per (row block, long | short chunks) group
+    int ngroups = 0;
+    int *gcnt = nullptr;         // symmetric kernel: [2 * nblocks] arrivals per group
+    int *gdone = nullptr;        // symmetric kernel: [2 * nblocks] group folded
+    double2 *slices = nullptr;   // symmetric kernel: [SYM_RING][SYM_RB] row sums per work item
+    double2 *rowsum = nullptr;   // symmetric kernel: [2][npad] row sums over the long / the short chunks
     NcclComm comm = nullptr;
     cudaGraphExec_t graph[2] = {nullptr, nullptr};   // indexed by the starting slot
 };
@@ -213,7 +219,7 @@ static ChunkMap choose_split_sym(int n, int requested)
 // waits on lower CTA indices only -- and the two are nv rows of items apart (8 rows on one GPU: the predecessor
 // finished long ago; one row on an 8-way shard: it started about half a CTA lifetime earlier).  The short items
 // still come last and fill the tail of the launch.
-static void sym_work_items(int n, const ChunkMap &cm, int v0, int nv, std::vector<int2> *items)
+static void sym_work_items(int n, const ChunkMap &cm, int v0, int nv, std::vector<int4> *items, std::vector<int2> *groups)
 {
     const int nblocks = (n + SYM_RB - 1) / SYM_RB;
     std::vector<int> rows;
@@ -224,26 +230,46 @@ static void sym_work_items(int n, const ChunkMap &cm, int v0, int nv, std::vecto
                 if (B < nblocks) rows.push_back(B);
             }
     items->clear();
+    groups->clear();
     for (int phase = 0; phase < 2; ++phase) {
         const int s_lo = phase == 0 ? 0 : cm.nbig;
         const int s_hi = phase == 0 ? cm.nbig : cm.nsplit;
         for (int B : rows) {
             int s = chunk_of(cm, B * SYM_RB);   // the chunk that holds the block's first row
             if (s < s_lo) s = s_lo;
-            for (; s < s_hi; ++s) items->push_back(make_int2(B, s));
+            if (s >= s_hi) continue;
+            const int g = static_cast<int>(groups->size());
+            groups->push_back(make_int2(static_cast<int>(items->size()), s_hi - s));
+            for (; s < s_hi; ++s) items->push_back(make_int4(B, s, g, -1));
         }
+    }
+    // Ring of row-sum slices: item i stores into slot i % SYM_RING unless it is its group's last item (that one
+    // folds).  Before it does, the fold of the group that read the slot's previous contents must be over.
+    std::vector<int> tenant(SYM_RING, -1);   // group of the last item that stored into the slot
+    for (size_t i = 0; i < items->size(); ++i) {
+        int4 &it = (*items)[i];
+        const int2 grp = (*groups)[it.z];
+        if (static_cast<int>(i) == grp.x + grp.y - 1) continue;   // folds, stores nothing
+        it.w = tenant[i % SYM_RING];
+        tenant[i % SYM_RING] = it.z;
     }
 }
 
 static int upload_sym_items(Shard &s, int n, const ChunkMap &cm, int v0, int nv)
 {
-    std::vector<int2> items;
-    sym_work_items(n, cm, v0, nv, &items);
+    std::vector<int4> items;
+    std::vector<int2> groups;
+    sym_work_items(n, cm, v0, nv, &items, &groups);
     if (s.items) cudaFree(s.items);
+    if (s.groups) cudaFree(s.groups);
     s.items = nullptr;
-    NB_CUDA(cudaMalloc(&s.items, sizeof(int2) * (items.empty() ? 1 : items.size())));
-    if (!items.empty()) NB_CUDA(cudaMemcpy(s.items, items.data(), sizeof(int2) * items.size(), cudaMemcpyHostToDevice));
+    s.groups = nullptr;
+    NB_CUDA(cudaMalloc(&s.items, sizeof(int4) * (items.empty() ? 1 : items.size())));
+    NB_CUDA(cudaMalloc(&s.groups, sizeof(int2) * (groups.empty() ? 1 : groups.size())));
+    if (!items.empty()) NB_CUDA(cudaMemcpy(s.items, items.data(), sizeof(int4) * items.size(), cudaMemcpyHostToDevice));
+    if (!groups.empty()) NB_CUDA(cudaMemcpy(s.groups, groups.data(), sizeof(int2) * groups.size(), cudaMemcpyHostToDevice));
     s.sym_items = static_cast<int>(items.size());
+    s.ngroups = static_cast<int>(groups.size());
     return NBODY_GPU_OK;
 }
 
@@ -285,6 +311,11 @@ static void free_shard(Shard &s)
     if (s.turn) cudaFree(s.turn);
     if (s.sym_err) cudaFree(s.sym_err);
     if (s.items) cudaFree(s.items);
+    if (s.groups) cudaFree(s.groups);
+    if (s.gcnt) cudaFree(s.gcnt);
+    if (s.gdone) cudaFree(s.gdone);
+    if (s.slices) cudaFree(s.slices);
+    if (s.rowsum) cudaFree(s.rowsum);
     if (s.flush) cudaFree(s.flush);
     if (s.orig) cudaFree(s.orig);
     if (s.mr0) cudaFree(s.mr0);
@@ -394,7 +425,11 @@ static int enqueue_forces(nbody_gpu *h, Shard &s, int slot, double2 *exact_out)
         SymArgs a;
         a.pos = s.pos[slot];
         a.mr = s.mr;
-        a.rowpart = s.part;
+        a.slices = s.slices;
+        a.rowsum = s.rowsum;
+        a.groups = s.groups;
+        a.gcnt = s.gcnt;
+        a.gdone = s.gdone;
         a.vacc = s.vacc;
         a.turn = s.turn;
         a.nseg = s.nseg;
@@ -429,7 +464,10 @@ static int enqueue_forces(nbody_gpu *h, Shard &s, int slot, double2 *exact_out)
 static void enqueue_sym_reduce(nbody_gpu *h, Shard &s, bool to_peers)
 {
     SymReduceArgs a;
-    a.rowpart = s.part;
+    a.rowsum = s.rowsum;
+    a.gcnt = s.gcnt;
+    a.gdone = s.gdone;
+    a.ngroups = 2 * h->nblocks;
     a.vacc = s.vacc;
     a.turn = s.turn;
     a.nseg = s.nseg;
@@ -1050,20 +1088,24 @@ int nbody_gpu_shard_plan(int n, int mode, int nranks, int rank, int out[8], long
     return NBODY_GPU_OK;
 }
 
-int nbody_gpu_sym_work_items(int n, int nranks, int rank, int *blocks, int *chunks, int cap, int *count,
-                             int *chunk_start_out, int chunk_cap, int *nchunks)
+int nbody_gpu_sym_work_items(int n, int nranks, int rank, int *blocks, int *chunks, int *groups_out, int *guards, int cap,
+                             int *count, int *chunk_start_out, int chunk_cap, int *nchunks, int *ring)
 {
     if (n < 1 || nranks < 1 || rank < 0 || rank >= nranks || cap < 0 || !count) return fail(NBODY_GPU_EINVAL, "bad argument");
     if (SYM_V % nranks != 0) return fail(NBODY_GPU_EINVAL, "the symmetric kernel shards over 1, 2, 4 or 8 GPUs");
     const ChunkMap cm = choose_split_sym(n, 0);
     const int nv = SYM_V / nranks;
-    std::vector<int2> items;
-    sym_work_items(n, cm, rank * nv, nv, &items);
+    std::vector<int4> items;
+    std::vector<int2> groups;
+    sym_work_items(n, cm, rank * nv, nv, &items, &groups);
     *count = static_cast<int>(items.size());
     for (int k = 0; k < *count && k < cap; ++k) {
         if (blocks) blocks[k] = items[k].x;
         if (chunks) chunks[k] = items[k].y;
+        if (groups_out) groups_out[k] = items[k].z;
+        if (guards) guards[k] = items[k].w;
     }
+    if (ring) *ring = SYM_RING;
     if (nchunks) *nchunks = cm.nsplit;
     if (chunk_start_out)
         for (int s = 0; s <= cm.nsplit && s < chunk_cap; ++s) {
@@ -1152,14 +1194,15 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
     const size_t bytes = sizeof(double2) * static_cast<size_t>(h->npad);
     if (h->symmetric) {
         h->cm = choose_split_sym(h->n, cfg->jsplit);
-        // the row-side partial sums grow with n * nsplit: when they do not fit the device, the
-        // directed kernel (2x the pair evaluations, fewer chunks) runs instead
+        // the symmetric kernel's scratch: reaction sums per owned virtual rank, two row-sum vectors, a fixed ring of
+        // slices -- O(n); the check stays for very large n
         const size_t slots = static_cast<size_t>(SYM_V / P);
         size_t free_b = 0, total_b = 0;
         if (multi_dev) NB_CUDA(cudaSetDevice(0));
         else if (cfg->device >= 0) NB_CUDA(cudaSetDevice(cfg->device));
         NB_CUDA(cudaMemGetInfo(&free_b, &total_b));
-        const double need = static_cast<double>(bytes) * (static_cast<double>(slots) + h->cm.nsplit + 24.0);
+        const double need = static_cast<double>(bytes) * (static_cast<double>(slots) + 2.0 + 24.0) +
+                            static_cast<double>(sizeof(double2)) * SYM_RING * SYM_RB;
         if (need > 0.92 * static_cast<double>(free_b)) {
             if (cfg->symmetric > 0)
                 return fail(NBODY_GPU_ENOMEM, "the symmetric kernel needs %.1f GB of partial sums for n = %d on %d GPU(s), %.1f GB are free",
@@ -1205,9 +1248,21 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
         NB_CUDA(cudaMemsetAsync(s.mr, 0, bytes, s.stream));
         NB_CUDA(cudaMalloc(&s.plan, sizeof(double) * 6 * static_cast<size_t>(h->npad)));
         if (fast) {
-            NB_CUDA(cudaMalloc(&s.part, bytes * h->nsplit));
-            NB_CUDA(cudaMemsetAsync(s.part, 0, bytes * h->nsplit, s.stream));
+            if (!h->symmetric) {   // directed kernel: one partial-sum vector per j-chunk
+                NB_CUDA(cudaMalloc(&s.part, bytes * h->nsplit));
+                NB_CUDA(cudaMemsetAsync(s.part, 0, bytes * h->nsplit, s.stream));
+            }
             if (h->symmetric) {
+                const size_t ring = sizeof(double2) * static_cast<size_t>(SYM_RING) * SYM_RB;
+                const size_t gwords = sizeof(int) * 2 * static_cast<size_t>(h->nblocks);
+                NB_CUDA(cudaMalloc(&s.slices, ring));
+                NB_CUDA(cudaMemsetAsync(s.slices, 0, ring, s.stream));
+                NB_CUDA(cudaMalloc(&s.rowsum, bytes * 2));
+                NB_CUDA(cudaMemsetAsync(s.rowsum, 0, bytes * 2, s.stream));   // rows without long (short) chunks stay 0
+                NB_CUDA(cudaMalloc(&s.gcnt, gwords));
+                NB_CUDA(cudaMemsetAsync(s.gcnt, 0, gwords, s.stream));
+                NB_CUDA(cudaMalloc(&s.gdone, gwords));
+                NB_CUDA(cudaMemsetAsync(s.gdone, 0, gwords, s.stream));
                 s.nv = SYM_V / P;
                 s.v0 = s.part_index * s.nv;
                 s.nseg = seg_count(h->cm);
@@ -1639,8 +1694,10 @@ int nbody_gpu_describe(const nbody_gpu *h, char *buf, int len)
                               h->sorted ? h->sort_interval : 0, h->sorts,
                               // device memory of the fast kernels' partial sums, per GPU: row sums per j-chunk, and the
                               // symmetric kernel's reaction sums per owned virtual rank
-                              !fast ? 0LL : static_cast<long long>(sizeof(double2)) * h->npad *
-                                  (h->nsplit + (h->symmetric ? h->shards[0].nv : 0)));
+                              !fast ? 0LL
+                              : h->symmetric ? static_cast<long long>(sizeof(double2)) *
+                                                   (static_cast<long long>(h->npad) * (h->shards[0].nv + 2) + static_cast<long long>(SYM_RING) * SYM_RB)
+                                             : static_cast<long long>(sizeof(double2)) * h->npad * h->nsplit);
     if (buf && len > 0) {
         strncpy(buf, tmp, static_cast<size_t>(len) - 1);
         buf[len - 1] = 0;

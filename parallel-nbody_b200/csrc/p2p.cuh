@@ -70,8 +70,9 @@ __global__ void __launch_bounds__(128) sym_reduce_p2p_kernel(const SymReduceArgs
     const double2 r = sym_take_reactions(a, j, blockIdx.y);
     double xf = r.x, yf = r.y;
     if (sym_vrank(blk) == v) {
-        for (int s = chunk_of(a.cm, blk * SYM_RB); s < a.cm.nsplit; ++s) {
-            const double2 c = a.rowpart[static_cast<size_t>(s) * a.npad + j];
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            const double2 c = a.rowsum[static_cast<size_t>(p) * a.npad + j];
             xf += c.x;
             yf += c.y;
         }

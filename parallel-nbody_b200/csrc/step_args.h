@@ -55,10 +55,18 @@ constexpr int SYM_SEG = 1024;
 __host__ __device__ inline int segs_per_chunk(const ChunkMap &m) { return (m.chunk + SYM_SEG - 1) / SYM_SEG; }
 __host__ __device__ inline int seg_count(const ChunkMap &m) { return m.nbig * segs_per_chunk(m) + (m.nsplit - m.nbig); }
 
+// Row sums: the CTAs of one row block (one "group": its long-chunk items, or its short-chunk items) leave their
+// SYM_RB row sums in a ring of SYM_RING slices (slot = CTA index % SYM_RING) and count themselves in; the group's
+// last CTA in dispatch order adds the slices in chunk order and writes the block's rows of rowsum[phase].
+constexpr int SYM_RING = 4096;
 struct SymArgs {
     const double2 *pos;
     const double2 *mr;
-    double2 *rowpart;     // [nsplit][npad]  row-side partial sums
+    double2 *slices;      // [SYM_RING][SYM_RB] row sums per work item, reused round the ring
+    double2 *rowsum;      // [2][npad] row sums over the long chunks / over the short chunks, chunk ascending
+    const int2 *groups;   // [ngroups] (first item, items) of every group
+    int *gcnt;            // [ngroups] items that have stored their slice       } zero at launch
+    int *gdone;           // [ngroups] 1 once the group's slices have been added } (sym_reduce_kernel leaves them so)
     // Reaction (column-side) sums: vacc[v - v0][j] collects, for virtual rank v, the reactions on body j from v's
     // row blocks below block(j), B ascending.  The CTAs of one (v, segment) chain add their share one after the
     // other: turn[(v - v0) * nseg + seg] counts the blocks that have added theirs (forces_sym.cuh).  Both are zero
@@ -75,8 +83,9 @@ struct SymArgs {
     // The grid holds live work items only, one CTA per item (x = row block, y = chunk), in dispatch order: row block
     // by row block (ascending) over the long chunks, then row block by row block over the short chunks -- the
     // predecessor of an item in its (v, segment) chain is at least a row of items ahead of it, and the short items
-    // still fill the tail of the launch.
-    const int2 *items;
+    // still fill the tail of the launch.  item = (row block, chunk, group, group whose fold must be over before this
+    // item may overwrite its ring slot, or -1).
+    const int4 *items;
 };
 constexpr int SYM_ERR_TURN = 16;
 
@@ -101,7 +110,9 @@ __host__ __device__ inline int sym_vrank_seq(int B)
     return 2 * (B / (2 * SYM_V)) + ((B % (2 * SYM_V)) < SYM_V ? 0 : 1);
 }
 struct SymReduceArgs {
-    const double2 *rowpart;
+    const double2 *rowsum; // [2][npad] the force kernel's row sums (long chunks, short chunks)
+    int *gcnt, *gdone;     // [ngroups] zeroed for the next launch
+    int ngroups;
     double2 *vacc;        // [nv][npad] reaction sums of the force kernel; read, then zeroed for the next launch
     int *turn;            // [nv][nseg] zeroed for the next launch
     int nseg;

@@ -31,7 +31,8 @@ def test_dispatch_order_feeds_every_chain_in_block_order(n, nranks):
     nblocks = -(-n // RB)
     seen_blocks = set()
     for rank in range(nranks):
-        blocks, chunks, start = nb.sym_work_items(n, nranks, rank)
+        w = nb.sym_work_items(n, nranks, rank)
+        blocks, chunks, start = w["blocks"], w["chunks"], w["chunk_start"]
         nchunks = len(start) - 1
         assert start[0] == 0 and start[-1] == n and np.all(np.diff(start) > 0)
         nv = V // nranks
@@ -73,6 +74,33 @@ def test_dispatch_order_feeds_every_chain_in_block_order(n, nranks):
                 gap = k - kp
                 min_gap = gap if min_gap is None else min(min_gap, gap)
         assert min_gap is None or min_gap >= 1
+        # row-sum groups: a row block's long-chunk items and its short-chunk items, each a run of consecutive items
+        # with the chunks ascending (the fold adds the slices in that order)
+        groups, guards, ring = w["groups"], w["guards"], w["ring"]
+        ngroups = int(groups.max()) + 1
+        first = np.full(ngroups, -1)
+        last = np.full(ngroups, -1)
+        for k, g in enumerate(groups.tolist()):
+            if first[g] < 0:
+                first[g] = k
+            assert last[g] in (-1, k - 1), "group %d is not a run of consecutive items" % g
+            last[g] = k
+            if k > first[g]:
+                assert blocks[k] == blocks[k - 1] and chunks[k] == chunks[k - 1] + 1
+            assert (lens[k] < lens[0]) == (lens[first[g]] < lens[0])      # long and short chunks do not mix
+        assert np.all(np.diff(first) > 0)                                   # group ids in dispatch order
+        # ring of slices: every item but its group's last (which folds) stores into slot k % ring; the guard is the
+        # group of the slot's previous tenant, and that group's fold (its last item) comes earlier in dispatch order
+        tenant = {}
+        for k, g in enumerate(groups.tolist()):
+            if k == last[g]:
+                assert guards[k] == -1
+                continue
+            want = tenant.get(k % ring, -1)
+            assert guards[k] == want
+            if want >= 0:
+                assert last[want] < k and want != g
+            tenant[k % ring] = g
     assert seen_blocks == set(range(nblocks))
 
 
