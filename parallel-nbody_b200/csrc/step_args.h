@@ -58,7 +58,10 @@ __host__ __device__ inline int seg_count(const ChunkMap &m) { return m.nbig * se
 // Row sums: the CTAs of one row block (one "group": its long-chunk items, or its short-chunk items) leave their
 // SYM_RB row sums in a ring of SYM_RING slices (slot = CTA index % SYM_RING) and count themselves in; the group's
 // last CTA in dispatch order adds the slices in chunk order and writes the block's rows of rowsum[phase].
-constexpr int SYM_RING = 4096;
+#ifndef NBODY_SYM_RING
+#define NBODY_SYM_RING 2048   // 16 MB of slices: a ring is 3.5 waves of CTAs long and short enough that a slice is overwritten before the L2 writes it back (profiles/r2_ring_sweep.log)
+#endif
+constexpr int SYM_RING = NBODY_SYM_RING;
 struct SymArgs {
     const double2 *pos;
     const double2 *mr;
