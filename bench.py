@@ -608,8 +608,9 @@ def main():
                        "n": n, "mode": args.mode, "parallelism": "row-shard x%d" % world,
                        "step_path": "CUDA graph of %d steps per launch" % desc["graph_steps"] if desc.get("graph_steps") else "plain launches",
                        "l2": "192 MiB scratch overwritten before every graph launch, inside the timed span (L2 flush); "
-                             "besides, every step streams its partial sums through the L2 (%s written and re-read per "
-                             "force launch, the L2 holds 126 MB)" % (mb(traffic) if traffic else "see roofline.traffic")},
+                             "the force kernel's partial sums (%s of device memory per GPU) are meant to live in the L2, "
+                             "its DRAM traffic per launch is roofline.traffic (%s)"
+                             % (mb(desc.get("partial_sum_bytes", 0)), mb(traffic) if traffic else "no capture for this configuration")},
             "steps_per_s": args.steps / (t_ms * 1e-3),
             "phase_ms_per_step": {"force": force_ms / args.steps, "integrate": integ_ms / args.steps,
                                   "exchange": exch_ms / args.steps, "whole_step_plain_launches": prof_ms / args.steps},
