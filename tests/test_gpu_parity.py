@@ -396,7 +396,8 @@ def test_pinned_host_buffers_round_trip(nb, oracle):
 @pytest.mark.parametrize("jsplit", [0, 1, 5])
 def test_reaction_sums_handed_from_cta_to_cta(nb, oracle, jsplit):
     """The symmetric kernel adds a row block's reaction sums to vacc[v][j] when it is that block's turn in the chain
-    of its (virtual rank, 1024-body segment) -- forces_sym.cuh.  Ragged N (last segment, tile and row block are
+    of its (virtual rank, 1024-body segment), and the last CTA of a row block folds the row sums its siblings left in
+    the slice ring -- forces_sym.cuh.  Ragged N (last segment, tile and row block are
     partial), chunk shapes with one segment per CTA (jsplit = 0: 1024-body chunks + one-tile chunks) and with many
     (jsplit = 1: one chunk of 41 segments; 5: 9 segments each): forces of block-boundary and random bodies against
     the oracle's row form (nbody-seq.c:87-107), and -- the order of the additions being fixed -- the same bits from
@@ -407,6 +408,8 @@ def test_reaction_sums_handed_from_cta_to_cta(nb, oracle, jsplit):
     g = make(nb, b, mode=nb.MODE_FAST, jsplit=jsplit)
     d = g.describe()
     assert d["symmetric"] and d["cell_order"], d
+    # the partial sums are O(N): 8 reaction vectors + 2 row-sum vectors + the fixed ring of slices
+    assert d["partial_sum_bytes"] <= 16 * 10 * (n + 8) + 16 * 512 * 4096, d
     order = oracle.cell_order(nb, b.x, b.y)
     rows = np.unique(np.concatenate([oracle.block_sample(order, per_block_extra=1), [0, 5, n - 1]])).astype(np.int32)
     wxf, wyf = oracle.forces_for(rows, b.x, b.y, b.mass, b.radius)
@@ -424,3 +427,22 @@ def test_reaction_sums_handed_from_cta_to_cta(nb, oracle, jsplit):
     for a, c in zip(g.fetch(), h.fetch()):
         assert np.array_equal(a.view(np.uint64), c.view(np.uint64))
     assert abs(fx.sum()) <= 1e-6 * np.abs(fx).sum() and abs(fy.sum()) <= 1e-6 * np.abs(fy).sum()   # Newton's third law
+
+
+def test_hand_overs_are_race_free_over_many_launches(nb, oracle):
+    """A race in the CTA-to-CTA hand-overs of the symmetric kernel (turn counters, slice ring reuse: the ring wraps
+    a dozen times per launch at this size, ragged N) would show as run-to-run differences in the last bits.  40
+    force launches on one handle, and the same 40 steps on a second handle split differently: identical bits."""
+    n = 150000 + 11
+    b = oracle.init_bodies(n)
+    g = make(nb, b, mode=nb.MODE_FAST)
+    h = make(nb, b, mode=nb.MODE_FAST)
+    g.step(40)
+    for k in (1, 7, 2, 30):
+        h.step(k)
+    for a, c in zip(g.fetch(), h.fetch()):
+        assert np.array_equal(a.view(np.uint64), c.view(np.uint64))
+    f1 = g.forces()
+    for _ in range(5):
+        f2 = g.forces()
+        assert np.array_equal(f1[0].view(np.uint64), f2[0].view(np.uint64)) and np.array_equal(f1[1].view(np.uint64), f2[1].view(np.uint64))
