@@ -24,8 +24,8 @@ right after the timed one: nbody_gpu_step_profiled, plain launches with an event
 peak = the DFMA rate measured live by nbody_gpu_fp64_peak (MEASURED_PEAKS.json has
 no FP64 figure).  pipe_frac = FP64-pipe instructions actually issued per pair (SASS count,
 confirmed by ncu sm__inst_executed_pipe_fp64) x pairs/s / (peak/2): the utilisation figure the
-north star's "% of FP64 pipe peak" means (the reciprocal square root makes one unordered pair 18 pipe
-instructions = 9 per interaction -- 16 = 8 in far-field tiles -- so the algorithmic-flop fraction cannot approach 1).
+north star's "% of FP64 pipe peak" means (the reciprocal square root makes one unordered pair 17 pipe
+instructions = 8.5 per interaction -- 15 = 7.5 in far-field tiles -- so the algorithmic-flop fraction cannot approach 1).
 traffic = DRAM bytes per force-kernel launch from the committed ncu captures (profiles/r2_traffic.json,
 written by tools/ncu_traffic.py from the .ncu-rep), keyed by kernel, N and GPU count.
 
@@ -360,7 +360,7 @@ def other_configs(nb, local_rank, peak_tf):
                                  "checked_by": "tests/test_gpu_parity.py::test_exact_4096_config2_prefix_and_graph_independence"}
     wall, dev, d, far = run(65536, nb.MODE_FAST, 200)
     rate = 200 * 65536 * 65535.0 / dev
-    ipp = 9.0 * (1.0 - far) + 8.0 * far
+    ipp = 8.5 * (1.0 - far) + 7.5 * far
     out["c3_65536x200_fast"] = {"seconds": wall, "ms_per_step": dev * 1e3 / 200, "steps_per_s": 200 / wall, "kernel": d["kernel"],
                                 "pair_interactions_per_s": rate, "far_field_fraction": far,
                                 "pipe_frac": ipp * rate / (peak_tf * 1e12 / 2.0),
@@ -557,8 +557,8 @@ def main():
     algo_tflops = 10.0 * launch_pairs / launch_s / 1e12   # reference flop model: 10 per directed pair
     ipp = desc.get("fp64_instr_per_pair") or None
     if ipp and far > 0.0:
-        # far-field tiles issue 16 FP64-pipe instructions per unordered pair instead of 18 (forces_sym.cuh)
-        ipp = ipp * (1.0 - far) + 8.0 * far
+        # far-field tiles issue 15 FP64-pipe instructions per unordered pair instead of 17 (forces_sym.cuh)
+        ipp = ipp * (1.0 - far) + 7.5 * far
     traffic, traffic_source = load_traffic(desc["kernel"], n, world)
     roofline = {"bound": "fp64", "achieved": algo_tflops, "peak": peak_tf, "unit": "TFLOP/s",
                 "frac": algo_tflops / peak_tf, "traffic": traffic, "traffic_source": traffic_source,

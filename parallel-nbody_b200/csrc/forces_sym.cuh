@@ -44,11 +44,15 @@
 // 1.92e-13, N = 262144: 1.97e-13; profiles/r2_error_table.log).  The kernel multiplies its sums by G anyway: folding
 // (1 + that mean) into the constant makes the pair terms unbiased at no cost, and the error of a body's force
 // drops from the bias (2e-13) to the zero-mean scatter.
+// The pair computes TWICE that value, y0*(3 - q*y0^2) = 2*y0*(1 + e/2), in three instructions (t = q*y0,
+// w = fma(-t, y0, 3), y0*w) instead of four; the sums are multiplied by G/2 at the end (exact halving), and the
+// re-scans of coincident bodies add twice their term.
 #if NBODY_SYM_RSQRT_ORDER >= 3
 #define NBODY_SYM_G NB_GRAVITY
 #else
 #define NBODY_SYM_G (NB_GRAVITY * (1.0 + 1.94e-13))
 #endif
+#define NBODY_SYM_GH (0.5 * NBODY_SYM_G)
 
 namespace nbody {
 
@@ -93,13 +97,14 @@ __device__ __forceinline__ void pair_sym(SymBody &b, double xj, double yj, doubl
     }
     const double y0 = (FLAVOR & 1) ? rsqrt_seed_donor(q, f2) : rsqrt_seed(q);
     const double t = q * y0;
+#if NBODY_SYM_RSQRT_ORDER >= 3
     const double e = fma(-t, y0, 1.0);       // 1 - q*y0^2; |e| < 4e-6 (seed: 2^-19, measured by tools/rsqrt_seed_probe.cu, + the donated low word: 2^-20)
     const double ye = y0 * e;
-#if NBODY_SYM_RSQRT_ORDER >= 3
-    const double p = fma(e, 0.375, 0.5);
-    const double y1 = fma(ye, p, y0);        // y0*(1 + e/2 + 3e^2/8) = 1 / (forced * sqrt(dsqr)) to ~1e-16
+    const double p = fma(e, 0.75, 1.0);
+    const double y1 = fma(ye, p, y0 + y0);   // 2*y0*(1 + e/2 + 3e^2/8) = 2 / (forced * sqrt(dsqr)) to ~1e-16
 #else
-    const double y1 = fma(ye, 0.5, y0);      // y0*(1 + e/2); the mean of the dropped term is folded into NBODY_SYM_G
+    const double w = fma(-t, y0, 3.0);       // 2 + e, e = 1 - q*y0^2, |e| < 4e-6
+    const double y1 = y0 * w;                // 2*y0*(1 + e/2); the mean of the dropped term is folded into NBODY_SYM_G
 #endif
     const double zi = mj * y1;
     b.ax = fma(zi, dx, b.ax);
@@ -125,14 +130,15 @@ __device__ __forceinline__ void pair_dir(SymBody &b, double xj, double yj, doubl
     const double q = fma(f2, dsqr, 1e-290);
     const double y0 = rsqrt_seed_donor(q, f2);   // the same seed as pair_sym: the same error distribution
     const double t = q * y0;
-    const double e = fma(-t, y0, 1.0);
     const double z0 = mj * y0;
-    const double ze = z0 * e;
 #if NBODY_SYM_RSQRT_ORDER >= 3
-    const double p = fma(e, 0.375, 0.5);
-    const double s = fma(ze, p, z0);
+    const double e = fma(-t, y0, 1.0);
+    const double ze = z0 * e;
+    const double p = fma(e, 0.75, 1.0);
+    const double s = fma(ze, p, z0 + z0);
 #else
-    const double s = fma(ze, 0.5, z0);
+    const double w = fma(-t, y0, 3.0);       // as in pair_sym: twice the term, G/2 at the end
+    const double s = z0 * w;
 #endif
     b.ax = fma(s, dx, b.ax);
     b.ay = fma(s, dy, b.ay);
@@ -359,7 +365,7 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
 #pragma unroll
             for (int k = 0; k < SYM_IB; ++k) {
                 if (b[k].minhi == 0) {
-                    b[k].ax += coincident_rescan(tp, tm, cnt, jb, idx[k], b[k].x, b[k].y, b[k].r);
+                    b[k].ax += 2.0 * coincident_rescan(tp, tm, cnt, jb, idx[k], b[k].x, b[k].y, b[k].r);
                     b[k].minhi = 0x7fffffff;
                 }
             }
@@ -402,7 +408,7 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
             for (int k = 0; k < SYM_IB; ++k) {
                 if (b[k].minhi == 0) {
                     if (idx[k] < a.n) {
-                        b[k].ax += sym_row_rescan(tp, tm, cnt, b[k].x, b[k].y, b[k].r);
+                        b[k].ax += 2.0 * sym_row_rescan(tp, tm, cnt, b[k].x, b[k].y, b[k].r);
                         hit = true;
                     }
                     b[k].minhi = 0x7fffffff;
@@ -421,8 +427,8 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
                 }
                 const double2 pj = tp[jt];
                 const double2 qj = tm[jt];
-                if (s_flag[tile & 1]) cx += sym_col_rescan(a.pos, a.mr, i0, i1, pj.x, pj.y, qj.y);
-                const double gmj = -NBODY_SYM_G * qj.x;
+                if (s_flag[tile & 1]) cx += 2.0 * sym_col_rescan(a.pos, a.mr, i0, i1, pj.x, pj.y, qj.y);
+                const double gmj = -NBODY_SYM_GH * qj.x;
                 s_seg[(jb - jc0) % SYM_SEG + jt] = make_double2(gmj * cx, gmj * cy);
             }
             if (tid == 0) s_flag[(tile + 1) & 1] = 0;
@@ -470,7 +476,7 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
             double2 *slice = a.slices + static_cast<size_t>(blockIdx.x % SYM_RING) * SYM_RB;
 #pragma unroll
             for (int k = 0; k < SYM_IB; ++k) {
-                const double gm = NBODY_SYM_G * b[k].m;
+                const double gm = NBODY_SYM_GH * b[k].m;
                 __stcg(slice + (idx[k] - i0), make_double2(gm * b[k].ax, gm * b[k].ay));
             }
             __syncthreads();
@@ -495,7 +501,7 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
 #pragma unroll
             for (int k = 0; k < SYM_IB; ++k) {
                 if (idx[k] < a.n) {
-                    const double gm = NBODY_SYM_G * b[k].m;
+                    const double gm = NBODY_SYM_GH * b[k].m;
                     out[idx[k]] = make_double2(sx[k] + gm * b[k].ax, sy[k] + gm * b[k].ay);
                 }
             }

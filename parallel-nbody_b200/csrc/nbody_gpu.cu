@@ -1677,7 +1677,7 @@ int nbody_gpu_describe(const nbody_gpu *h, char *buf, int len)
     // FP64-pipe instructions per directed pair-interaction (SASS counts): the symmetric
     // kernel issues 18 per unordered pair = 2 interactions (16 in far-field tiles: see nbody_gpu_far_fraction);
     // exact mode is not a fixed count (divisions, branches)
-    const double ipp = !fast ? 0.0 : h->symmetric ? 9.0 : 16.0;
+    const double ipp = !fast ? 0.0 : h->symmetric ? 8.5 : 16.0;   // per directed interaction: 17 per unordered near-field pair (15 far field)
     const int graph = h->small ? 0 : ((!h->sharded || h->p2p) ? h->graph_steps : 0);
     char tmp[768];
     const int need = snprintf(tmp, sizeof tmp,
