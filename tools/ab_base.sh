@@ -1,6 +1,8 @@
 #!/bin/bash
 # development aid, one gpurun call: bits (tools/state_hash.py) and times of this build against an earlier build kept
 # under tools/_ab/ (libnbody_gpu_base.so, libnbody_gpu_dev_base.so; git-ignored, they travel with gpurun)
+# (build them from the commit to compare with: git worktree add /tmp/basewt <commit>; make -C /tmp/basewt/parallel-nbody_b200/csrc all dev;
+#  cp the two .so files to tools/_ab/libnbody_gpu_base.so and tools/_ab/libnbody_gpu_dev_base.so)
 set -u
 mkdir -p gpurun_out
 BASE=$PWD/tools/_ab/libnbody_gpu_base.so
