@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define NBODY_GPU_ABI_VERSION 4
+#define NBODY_GPU_ABI_VERSION 5
 
 enum {
     NBODY_GPU_OK = 0,
@@ -120,6 +120,33 @@ int nbody_gpu_step_profiled(nbody_gpu *h, int steps, int flush_l2, float out_ms[
  * current positions, into xf/yf; the handle's state -- including the last step's forces that
  * nbody_gpu_fetch returns -- is untouched.  Synchronous. */
 int nbody_gpu_forces(nbody_gpu *h, double *xf, double *yf);
+
+/* No counterpart in the reference (which owns all of its memory and has no accelerator): a force pass for callers
+ * that are not allowed to allocate device memory.  Typical ones: a plug-in inside an application whose own pool
+ * took the GPU's memory at start-up, so cudaMalloc has nothing to give or is reserved for the host application;
+ * and a latency-sensitive loop that cannot afford cudaMalloc/cudaFree, either of which may wait for every stream
+ * on the device.  The call itself performs no cudaMalloc, cudaFree or other allocating call.
+ *
+ * It is compute_forces in fast mode (clear_forces + compute_forces, nbody-seq.c:458-459, evaluated pair by pair in
+ * both directions like nbody_gpu_forces on a handle with cfg.symmetric = -1, cfg.sort = -1 and the default jsplit:
+ * same kernels, same chunks, same bits), but on the CALLER'S DEVICE arrays, in the library's device layout:
+ *     pos_xy      [2n] x0 y0 x1 y1 ...            (read)
+ *     mass_radius [2n] m0 R0 m1 R1 ...            (read)
+ *     force_xy    [2n] xf0 yf0 xf1 yf1 ...        (written)
+ * all three 16-byte aligned device memory of the CURRENT device; `stream` is a cudaStream_t passed as a pointer
+ * (NULL = the default stream).  The kernels are only enqueued: force_xy is valid once the stream has caught up.
+ *
+ * The per-chunk partial sums, which a handle keeps in memory it allocates, live in one fixed array built into the
+ * library: NBODY_GPU_STATIC_SCRATCH_BYTES on every GPU that loads the library, for the life of the process.  That
+ * is why n is limited to NBODY_GPU_STATIC_MAX_BODIES; a larger n is refused with NBODY_GPU_EINVAL and a message.
+ *  - The first call on each device looks up the array's device address (a one-off set-up step): make that first
+ *    call during start-up, before any stream capture begins.
+ *  - All calls on a device share the one array.  A call reads only what it has itself written, so nothing needs
+ *    clearing between calls, but two calls whose kernels overlap on the GPU (different streams without an
+ *    ordering between them) race on it and both results are garbage: keep calls on one stream or order them. */
+#define NBODY_GPU_STATIC_MAX_BODIES 32768
+#define NBODY_GPU_STATIC_SCRATCH_BYTES (16u << 20)
+int nbody_gpu_forces_static(int n, const double *pos_xy, const double *mass_radius, double *force_xy, void *stream);
 
 /* Replaces reading world->bodies after the loop (print(), nbody-seq.c:356-365):
  * waits for the queue, then copies the CURRENT positions, the last step's forces and

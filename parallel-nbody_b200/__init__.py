@@ -20,6 +20,8 @@ LIB_PATH = os.environ.get("NBODY_GPU_LIB") or os.path.join(_HERE, "libnbody_gpu.
 MODE_EXACT = 0
 MODE_FAST = 1
 NCCL_ID_BYTES = 128
+STATIC_MAX_BODIES = 32768          # NBODY_GPU_STATIC_MAX_BODIES
+STATIC_SCRATCH_BYTES = 16 << 20     # NBODY_GPU_STATIC_SCRATCH_BYTES
 
 _dp = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
 
@@ -91,6 +93,7 @@ def lib():
     if not os.environ.get("NBODY_GPU_LIB") or hasattr(L, "nbody_gpu_sym_work_items"):   # an older build under A/B test may lack it
         L.nbody_gpu_sym_work_items.argtypes = [ci, ci, ci, ip, ip, ip, ip, ci, ip, ip, ci, ip, ip]
     L.nbody_gpu_pin_host.argtypes = [vp, ctypes.c_size_t]
+    L.nbody_gpu_forces_static.argtypes = [ci, vp, vp, vp, vp]
     L.nbody_gpu_unpin_host.argtypes = [vp]
     _lib = L
     return L
@@ -122,6 +125,15 @@ def partition_reference(n, nranks):
     displs = (ctypes.c_int * nranks)()
     lib().nbody_gpu_partition_reference(n, nranks, counts, displs)
     return list(counts), list(displs)
+
+
+def forces_static(n, pos_xy_ptr, mass_radius_ptr, force_xy_ptr, stream=None):
+    """nbody_gpu_forces_static: the fast-mode force pass on DEVICE arrays the caller owns (integer addresses:
+    interleaved x/y, mass/radius in, xf/yf out; 2n doubles each, 16-byte aligned, on the current device), enqueued
+    on `stream` (a cudaStream_t as an integer; None = the default stream).  Allocates nothing -- the partial sums
+    sit in a fixed array inside the library -- so n may not exceed STATIC_MAX_BODIES.  For callers whose device
+    memory belongs to someone else's pool, or who cannot afford a cudaMalloc stall inside their loop."""
+    _check(lib().nbody_gpu_forces_static(int(n), pos_xy_ptr, mass_radius_ptr, force_xy_ptr, stream))
 
 
 def shard_plan(n, mode, nranks, rank):

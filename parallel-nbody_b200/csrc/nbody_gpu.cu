@@ -13,7 +13,9 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <cstdint>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -1787,3 +1789,112 @@ long long nbody_gpu_launch_count(const nbody_gpu *h, long long out[4])
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------
+// nbody_gpu_forces_static: the directed fast-mode force pass for callers that must not allocate.
+//
+// Who that is: a host program whose device memory was carved up once, at start-up, by somebody else's pool (a
+// simulation framework, an inference server sharing the GPU) so that the driver's allocator has nothing left or
+// is off limits to plug-ins; and a per-frame or per-request loop in which a cudaMalloc or cudaFree -- both may wait
+// for the whole device -- is a stall other streams would feel.  Such a caller already owns its position and force
+// buffers; what it cannot supply is the kernel's scratch: the directed kernel leaves one partial force vector per
+// j-chunk (forces_fast.cuh) that a second kernel adds up in chunk order.  Here that scratch is g_static_part,
+// a fixed array inside the library image.  Every GPU whose context loads the library carries its
+// NBODY_GPU_STATIC_SCRATCH_BYTES (16 MiB) until the process ends, used or not -- hence the modest limit of
+// NBODY_GPU_STATIC_MAX_BODIES bodies.
+//
+// g_static_part, named in HOST code, is only the host-side shadow of the symbol, never a device address; the
+// kernels are handed what cudaGetSymbolAddress returns, asked once per device with that device current.
+// ---------------------------------------------------------------------------------------------------------
+constexpr size_t STATIC_PART_ELEMS = NBODY_GPU_STATIC_SCRATCH_BYTES / sizeof(double2);
+static __device__ __align__(256) double2 g_static_part[STATIC_PART_ELEMS];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+static std::mutex g_static_mutex;
+static double2 *g_static_part_addr[STATIC_MAX_DEVICES] = {};   // device address of g_static_part on each device
+
+// Device address of the scratch array on the CURRENT device `dev` (looked up on the first call per device).
+static int static_part_address(int dev, double2 **out)
+{
+    if (dev < 0 || dev >= STATIC_MAX_DEVICES)
+        return fail(NBODY_GPU_EINVAL, "device ordinal %d outside 0..%d", dev, STATIC_MAX_DEVICES - 1);
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_part_addr[dev]) {
+        void *p = nullptr;
+        NB_CUDA(cudaGetSymbolAddress(&p, g_static_part));
+        if (!p) return fail(NBODY_GPU_ECUDA, "cudaGetSymbolAddress returned no address for the static scratch");
+        g_static_part_addr[dev] = static_cast<double2 *>(p);
+    }
+    *out = g_static_part_addr[dev];
+    return NBODY_GPU_OK;
+}
+
+static int check_device_array(const void *p, int dev, const char *what)
+{
+    if (!p) return fail(NBODY_GPU_EINVAL, "%s is NULL", what);
+    if (reinterpret_cast<uintptr_t>(p) % sizeof(double2))
+        return fail(NBODY_GPU_EINVAL, "%s is not 16-byte aligned", what);
+    cudaPointerAttributes at;
+    NB_CUDA(cudaPointerGetAttributes(&at, p));
+    if (at.type != cudaMemoryTypeDevice && at.type != cudaMemoryTypeManaged)
+        return fail(NBODY_GPU_EINVAL, "%s is not device memory (this entry point takes DEVICE pointers)", what);
+    if (at.type == cudaMemoryTypeDevice && at.device != dev)
+        return fail(NBODY_GPU_EINVAL, "%s lives on device %d, the current device is %d", what, at.device, dev);
+    return NBODY_GPU_OK;
+}
+
+extern "C" int nbody_gpu_forces_static(int n, const double *pos_xy, const double *mass_radius, double *force_xy,
+                                       void *stream)
+{
+    if (n < 1) return fail(NBODY_GPU_EINVAL, "n = %d: need at least one body", n);
+    if (n > NBODY_GPU_STATIC_MAX_BODIES)
+        return fail(NBODY_GPU_EINVAL,
+                    "n = %d exceeds NBODY_GPU_STATIC_MAX_BODIES = %d: the built-in scratch array of %zu bytes cannot "
+                    "hold the partial sums; use a handle (nbody_gpu_init + nbody_gpu_forces), which allocates",
+                    n, NBODY_GPU_STATIC_MAX_BODIES, static_cast<size_t>(NBODY_GPU_STATIC_SCRATCH_BYTES));
+    int nsplit = 1, chunk = n;
+    choose_split(n, 0, &nsplit, &chunk);   // the library default of a handle: same chunks, same summation order
+    const int npad = (n + 15) / 16 * 16;
+    if (static_cast<size_t>(nsplit) * npad > STATIC_PART_ELEMS)
+        return fail(NBODY_GPU_EINVAL, "n = %d needs %d partial vectors of %d: more than the built-in scratch holds",
+                    n, nsplit, npad);
+    int dev = -1;
+    NB_CUDA(cudaGetDevice(&dev));
+    int rc = check_device_array(pos_xy, dev, "pos_xy");
+    if (!rc) rc = check_device_array(mass_radius, dev, "mass_radius");
+    if (!rc) rc = check_device_array(force_xy, dev, "force_xy");
+    if (rc) return rc;
+    double2 *part = nullptr;
+    rc = static_part_address(dev, &part);
+    if (rc) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+    // Nothing in the array has to start at zero: every (chunk, row < n) element the fold reads is stored by the
+    // force kernel of this same call first (a CTA of an empty chunk stores zeros), so the leftovers of earlier
+    // calls are never read.
+    ForceArgs fa;
+    fa.pos = reinterpret_cast<const double2 *>(pos_xy);
+    fa.mr = reinterpret_cast<const double2 *>(mass_radius);
+    fa.out = part;
+    fa.n = n;
+    fa.npad = npad;
+    fa.lo = 0;
+    fa.hi = n;
+    fa.chunk = chunk;
+    launch_forces_fast(fa, nsplit, st);
+    NB_CUDA(cudaGetLastError());
+
+    IntegrateArgs ia;
+    memset(&ia, 0, sizeof ia);
+    ia.part = part;
+    ia.vbuf = nullptr;
+    ia.frc = reinterpret_cast<double2 *>(force_xy);
+    ia.nsplit = nsplit;
+    ia.npad = npad;
+    ia.n = n;
+    ia.lo = 0;
+    ia.hi = n;
+    launch_reduce_fast(ia, st);   // partial vectors, chunk ascending -> force_xy
+    NB_CUDA(cudaGetLastError());
+    return NBODY_GPU_OK;
+}

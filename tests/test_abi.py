@@ -22,7 +22,7 @@ def test_library_exports_every_declared_symbol(nb):
     assert len(names) >= 15
     for nm in names:
         assert hasattr(L, nm), nm
-    assert L.nbody_gpu_abi_version() == 4
+    assert L.nbody_gpu_abi_version() == 5
 
 
 def test_header_compiles_as_c(tmp_path):
