@@ -213,6 +213,13 @@ static ChunkMap choose_split_sym(int n, int requested)
     return m;
 }
 
+// The ring of row-sum slices (SYM_RING slots, slot = item index % SYM_RING) is only safe while no group -- at most
+// all long chunks, or all short chunks, of one row block -- has more than SYM_RING items: with a longer one, item
+// i + SYM_RING of the group would have to wait for the fold of its OWN group before overwriting item i's slot, and
+// that fold waits for it.  With the default split this is n > ~16.7 million bodies, or a requested jsplit > SYM_RING.
+static int sym_max_group(const ChunkMap &cm) { return cm.nbig > cm.nsplit - cm.nbig ? cm.nbig : cm.nsplit - cm.nbig; }
+static bool sym_ring_fits(const ChunkMap &cm) { return sym_max_group(cm) <= SYM_RING; }
+
 // Work items of the symmetric kernel for a device that owns virtual ranks [v0, v0 + nv): every (owned row block,
 // chunk) pair whose chunk reaches above the block's first row, in dispatch order -- the long chunks row block by row
 // block, then the short chunks row block by row block.  The row blocks of a group of 2*SYM_V go in the order
@@ -1056,7 +1063,7 @@ int nbody_gpu_shard_plan(int n, int mode, int nranks, int rank, int out[8], long
     int lo = 0, hi = 0;
     partition(n, nranks, rank, &lo, &hi);
     const bool fast = mode == NBODY_GPU_MODE_FAST;
-    const bool symmetric = fast && (SYM_V % nranks == 0) && n >= 8192;
+    const bool symmetric = fast && (SYM_V % nranks == 0) && n >= 8192 && sym_ring_fits(choose_split_sym(n, 0));
     for (int k = 0; k < 8; ++k) out[k] = 0;
     out[0] = lo;
     out[1] = hi;
@@ -1096,6 +1103,9 @@ int nbody_gpu_sym_work_items(int n, int nranks, int rank, int *blocks, int *chun
     if (n < 1 || nranks < 1 || rank < 0 || rank >= nranks || cap < 0 || !count) return fail(NBODY_GPU_EINVAL, "bad argument");
     if (SYM_V % nranks != 0) return fail(NBODY_GPU_EINVAL, "the symmetric kernel shards over 1, 2, 4 or 8 GPUs");
     const ChunkMap cm = choose_split_sym(n, 0);
+    if (!sym_ring_fits(cm))
+        return fail(NBODY_GPU_EINVAL, "n = %d: a row block would have %d items, the slice ring holds %d (the library uses the "
+                    "directed kernel for such n)", n, sym_max_group(cm), SYM_RING);
     const int nv = SYM_V / nranks;
     std::vector<int4> items;
     std::vector<int2> groups;
@@ -1196,6 +1206,15 @@ static int init_impl(nbody_gpu *h, const nbody_gpu_cfg *cfg, const double *x, co
     const size_t bytes = sizeof(double2) * static_cast<size_t>(h->npad);
     if (h->symmetric) {
         h->cm = choose_split_sym(h->n, cfg->jsplit);
+        if (!sym_ring_fits(h->cm)) {   // a row block's items would wrap round the slice ring onto themselves
+            if (cfg->symmetric > 0)
+                return fail(NBODY_GPU_EINVAL, "the symmetric kernel cannot split n = %d into %d chunks per row block: its ring "
+                            "holds %d row-sum slices (use a smaller jsplit, or symmetric = 0 for the directed kernel)",
+                            h->n, sym_max_group(h->cm), SYM_RING);
+            h->symmetric = false;
+        }
+    }
+    if (h->symmetric) {
         // the symmetric kernel's scratch: reaction sums per owned virtual rank, two row-sum vectors, a fixed ring of
         // slices -- O(n); the check stays for very large n
         const size_t slots = static_cast<size_t>(SYM_V / P);

@@ -110,3 +110,28 @@ def test_sym_work_items_rejects_bad_arguments():
         nb.sym_work_items(65536, 3, 0)      # 3 does not divide the 8 virtual ranks
     with pytest.raises(nb.NBodyGPUError):
         nb.sym_work_items(65536, 2, 2)
+
+
+def test_groups_longer_than_the_slice_ring_are_refused():
+    """A row block with more items than the ring has slots would wait for its own fold (item k + ring shares item
+    k's slot and group): the library must not build such a table.  With the default split that is n above ~16.7
+    million; the plan then names the directed kernel, and the table is refused."""
+    nb = pnb200.load()
+    ring = 2048
+    n_ok, n_big = ring * 8192, (ring + 2) * 8192
+    assert nb.shard_plan(n_ok, nb.MODE_FAST, 8, 0)["symmetric"]
+    assert nb.shard_plan(n_ok, nb.MODE_FAST, 8, 0)["chunks"] - nb.shard_plan(n_ok, nb.MODE_FAST, 8, 0)["long_chunks"] <= ring
+    assert not nb.shard_plan(n_big, nb.MODE_FAST, 8, 0)["symmetric"]
+    with pytest.raises(nb.NBodyGPUError, match="slice ring"):
+        nb.sym_work_items(n_big, 8, 0)
+
+
+@pytest.mark.gpu
+def test_init_refuses_a_split_that_wraps_the_slice_ring():
+    """cfg.jsplit beyond the ring size with the symmetric kernel insisted on: EINVAL at init instead of a step that
+    spins until its timeout; without the insistence the handle takes the directed kernel."""
+    nb = pnb200.load()
+    n = 4096 * 512
+    x, y, xv, yv, m, r = nb.reference_init(n)
+    with pytest.raises(nb.NBodyGPUError, match="ring"):
+        nb.NBodyGPU(x, y, xv, yv, m, r, mode=nb.MODE_FAST, device=0, symmetric=1, jsplit=4096)
