@@ -20,6 +20,16 @@
  *
  * Threading: one host thread drives a handle (the reference's step loop has one
  * caller thread per rank).  nbody_gpu_step only enqueues; fetch/sync wait.
+ *
+ * COLLECTIVE CALLS.  In a multi-process job (cfg.nranks > 1) the ranks are the reference's MPI ranks and, like
+ * MPI collectives, these calls must be made by EVERY rank, in the same order, with the same arguments NULL or
+ * non-NULL: nbody_gpu_init, nbody_gpu_set_state, nbody_gpu_step (and _timed/_bench/_profiled) with the same step
+ * count, nbody_gpu_forces, nbody_gpu_fetch, nbody_gpu_fetch_range, nbody_gpu_destroy.
+ * The reference's "rank 0 prints" pattern therefore becomes "every rank fetches, rank 0 prints".  The GPUs meet
+ * at barriers inside these calls; a rank that does not turn up within 30 s (wall time) is taken for dead: the
+ * waiting GPUs raise an error, every rank's handle is poisoned and the next synchronising call reports
+ * "peer exchange timed out".  Host-side work between two collective calls (I/O, a check) may differ between ranks
+ * by less than that.  Not collective: nbody_gpu_sync, nbody_gpu_describe, nbody_gpu_launch_count, the host helpers.
  */
 #ifndef NBODY_GPU_H
 #define NBODY_GPU_H
@@ -170,7 +180,7 @@ int nbody_gpu_fetch_range(nbody_gpu *h, int first, int count, double *x, double 
 int nbody_gpu_render(nbody_gpu *h, unsigned char *rgb);
 
 /* Fraction of the symmetric kernel's pair evaluations (tiles above the diagonal) that currently take the
- * far-field form (no clamp, 17 instead of 19 FP64-pipe instructions); 0 when the handle is not in cell order.
+ * far-field form (no clamp, 15 instead of 17 FP64-pipe instructions); 0 when the handle is not in cell order.
  * For bench.py's instruction accounting.  Synchronous. */
 int nbody_gpu_far_fraction(nbody_gpu *h, double *fraction);
 

@@ -20,14 +20,14 @@
 // than any r_i + r_j of their bodies.  Every tile carries a bounding box (x/y range, largest radius; one more
 // TMA copy per tile); if the gap between the block's box and the tile's box is at least rmax_B + rmax_T the
 // clamp max(dsqr, mindsqr) is the identity for every pair of the tile and no two bodies can coincide, so the
-// tile runs the far-field form of the pair: 16 FP64-pipe instructions and no integer work.  The test uses the
+// tile runs the far-field form of the pair: 15 FP64-pipe instructions and no integer work.  The test uses the
 // same rounded operations as the pair itself (monotone), so it is exact and both forms give the same bits.
 // Row sums: the CTAs of one row block leave their sums in a ring of slices and count themselves in; the block's last
 // CTA in dispatch order waits for the count and adds the slices in chunk order (rowsum[phase][i]; a small ring that
 // stays in the L2 instead of one N-vector per j-chunk in HBM).
 // sym_reduce_kernel then adds each body's row sums to its block's virtual rank: SYM_V per-virtual-rank vectors
 // (step_args.h), and integrate_kernel adds those in a fixed order: the same bits on 1, 2, 4 or 8 GPUs.
-// Per unordered pair: 18 FP64-pipe instructions (16 in far-field tiles) + 1 MUFU + 1.5 .. 6 ALU/LSU/SHFL, against
+// Per unordered pair: 17 FP64-pipe instructions (15 in far-field tiles) + 1 MUFU + 1.5 .. 6 ALU/LSU/SHFL, against
 // 2 x (16 + ...) for the directed kernel.
 #pragma once
 #include <cuda_runtime.h>
@@ -193,17 +193,33 @@ static_assert(SYM_RB % TILE_J == 0, "row blocks must be tile aligned");
 static_assert(SYM_SEG % TILE_J == 0 && SYM_SEG % SYM_RB == 0, "segments are whole tiles and whole row blocks");
 
 // A CTA's turn in its (virtual rank, segment) chain: wait until the `seq` blocks before it have added their sums.
-// The CTA waited for has a lower blockIdx (dispatched earlier), so it is running or done; the wait still gives up
-// after ~4 s (a lost predecessor must not hang the device) and raises the error word.
+// ASSUMPTION (not a CUDA guarantee): CTAs start in ascending blockIdx order, so the CTA waited for -- always one
+// with a lower index (tests/test_sym_items.py checks the table) -- is running or done.  Every GPU so far dispatches
+// that way; should one not, the wait gives up after SYM_WAIT_NS of wall time (%globaltimer: a debugger, a
+// time-sliced GPU or a profiler stretch cycles, not this limit) or as soon as another CTA has given up, and raises
+// the error word.  From then on the step is lost: later force CTAs, the fold and integrate_kernel return at once
+// (so the state stays that of the last good step), and the host reports the failure at its next synchronisation.
+constexpr unsigned long long SYM_WAIT_NS = 4000000000ULL;
+__device__ __forceinline__ unsigned long long wall_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 __device__ __forceinline__ void turn_wait(const int *turn, int seq, int *error_word)
 {
     int v;
     asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(turn) : "memory");
     if (v == seq) return;
-    for (unsigned spins = 0; spins < (1u << 24); ++spins) {
+    const unsigned long long t0 = wall_ns();
+    for (unsigned spins = 0;; ++spins) {
         __nanosleep(spins < 64 ? 32 : 256);
         asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(turn) : "memory");
         if (v == seq) return;
+        if ((spins & 255u) == 255u) {
+            if (*reinterpret_cast<volatile int *>(error_word) != 0) return;   // somebody else gave up already
+            if (wall_ns() - t0 > SYM_WAIT_NS) break;
+        }
     }
     atomicExch(error_word, SYM_ERR_TURN);
 }
@@ -275,6 +291,7 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
     const int warp = tid >> 5;
     // grid = the live (row block, chunk) items in dispatch order (SymArgs::items): no CTA is launched for a chunk that
     // lies entirely below its row block
+    if (*reinterpret_cast<volatile const int *>(a.error_word) != 0) return;   // a hand-over failed earlier: the step is lost
     const int4 item = a.items[blockIdx.x];
     const int blk = item.x;   // row block index
     const int by = item.y;    // chunk index

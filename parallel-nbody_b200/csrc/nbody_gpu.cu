@@ -410,6 +410,7 @@ static IntegrateArgs integrate_args(const nbody_gpu *h, const Shard &s, int slot
     a.xdim = h->cfg.xdim;
     a.ydim = h->cfg.ydim;
     a.npeers = 0;
+    a.error_word = s.sym_err;
     a.boxes = h->fused_boxes ? s.boxes : nullptr;
     for (int r = 0; r < MAX_PEERS; ++r) {
         a.peer_pos_new[r] = nullptr;
@@ -1696,7 +1697,7 @@ int nbody_gpu_describe(const nbody_gpu *h, char *buf, int len)
                          : h->symmetric ? (h->n >= SYM_WIDE_N ? "forces_sym_kernel<64,8>" : "forces_sym_kernel<128,4>")
                                         : "forces_fast_kernel<2,4,1,true>";
     // FP64-pipe instructions per directed pair-interaction (SASS counts): the symmetric
-    // kernel issues 18 per unordered pair = 2 interactions (16 in far-field tiles: see nbody_gpu_far_fraction);
+    // kernel issues 17 per unordered pair = 2 interactions (15 in far-field tiles: see nbody_gpu_far_fraction);
     // exact mode is not a fixed count (divisions, branches)
     const double ipp = !fast ? 0.0 : h->symmetric ? 8.5 : 16.0;   // per directed interaction: 17 per unordered near-field pair (15 far field)
     const int graph = h->small ? 0 : ((!h->sharded || h->p2p) ? h->graph_steps : 0);

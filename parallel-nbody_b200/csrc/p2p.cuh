@@ -11,8 +11,8 @@
 // (PeerTable::epoch) and is advanced by the kernel itself, so the launch arguments never change and the whole
 // sharded step loop can sit in a CUDA graph.  Positions are double-buffered and the two barriers order the
 // reuse of vbuf, so no buffer is overwritten while a peer still reads it.
-// A wait gives up after ~10 s, raises an error word and poisons every peer's flags so that the other GPUs stop
-// at once instead of waiting out their own 10 s.
+// A wait gives up after P2P_WAIT_NS (30 s of wall time), raises an error word and poisons every peer's flags so
+// that the other GPUs stop at once instead of waiting out their own limit.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -21,6 +21,10 @@
 namespace nbody {
 
 constexpr unsigned long long P2P_POISON = ~0ULL;
+// How long a GPU waits for a peer at a barrier before it declares the job dead.  The barriers sit in the step, so
+// this also bounds the host-side skew between ranks of a multi-process job (one rank instantiating a graph, doing
+// I/O or a check between two collective calls): 30 s of wall time (%globaltimer).
+constexpr unsigned long long P2P_WAIT_NS = 30000000000ULL;
 
 __global__ void __launch_bounds__(32) p2p_barrier_kernel(const PeerTable t, int phase, int *error_word)
 {
@@ -39,14 +43,19 @@ __global__ void __launch_bounds__(32) p2p_barrier_kernel(const PeerTable t, int 
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(e) : "memory");
     // wait for peer r's signal
     const unsigned long long *src = t.flags[t.me] + phase * MAX_PEERS + r;
-    const long long t0 = clock64();
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
     unsigned long long v = 0;
-    for (;;) {
+    for (unsigned spins = 0;; ++spins) {
         asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(src) : "memory");
         if (v >= e) break;
-        if (clock64() - t0 > 20000000000LL) {   // ~10 s at 1.9 GHz: a peer never arrived
-            v = P2P_POISON;
-            break;
+        if ((spins & 1023u) == 1023u) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (now - t0 > P2P_WAIT_NS) {   // wall time, whatever the SM clock: a peer never arrived
+                v = P2P_POISON;
+                break;
+            }
         }
         __nanosleep(200);
     }

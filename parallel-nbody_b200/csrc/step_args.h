@@ -158,6 +158,8 @@ struct IntegrateArgs {
     double *boxes;                      // fused tile boxes of the NEW positions (cell order; lo % TILE_J == 0), or nullptr
     double *peer_boxes[MAX_PEERS];      // with the fused exchange: every device's box array
     int npeers;                         // 0 = store to pos_new / boxes only
+    const int *error_word;              // device error word of the symmetric kernel / peer barriers (nullptr: none): once it is
+                                        // nonzero the step is lost and integrate_kernel leaves the state as it is
 };
 
 // Cell order (kernels_sort.cu): key = Hilbert index of the position << 32 | original index, value = slot.

@@ -288,6 +288,8 @@ __global__ void __launch_bounds__(TILE_J) integrate_kernel(const IntegrateArgs a
 {
     __shared__ double s_tab[(MODE == MODE_EXACT) ? NBODY_DM_ATAN_TAB_LEN : 1];
     __shared__ double s_red[(MODE == MODE_FAST) ? 5 : 1][TILE_J / 32];
+    // a force-kernel hand-over or a peer barrier gave up: do not integrate garbage (uniform over the CTA)
+    if (a.error_word && *reinterpret_cast<volatile const int *>(a.error_word) != 0) return;
     if (MODE == MODE_EXACT) {
         for (int k = threadIdx.x; k < NBODY_DM_ATAN_TAB_LEN; k += blockDim.x) s_tab[k] = c_atan_tab[k];
         __syncthreads();
