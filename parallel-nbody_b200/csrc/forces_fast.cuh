@@ -72,8 +72,10 @@ __device__ __forceinline__ void pair_fast2(FastBody &b, double xj, double yj, do
 }
 
 // Rare path: add the reference's (+-force, 0) for bodies j coincident with body i.
+// `orig` (slot -> original body index, or nullptr when the arrays are in creation order): the convention is about
+// ORIGINAL indices, also for bodies that became coincident after the last re-sort of a cell-ordered handle.
 __device__ __noinline__ double coincident_rescan(const double2 *s_pos, const double2 *s_mr, int cnt, int jb, int i,
-                                                 double xi, double yi, double ri)
+                                                 double xi, double yi, double ri, const int *orig = nullptr)
 {
     double ax = 0.0;
     for (int jj = 0; jj < cnt; ++jj) {
@@ -83,7 +85,8 @@ __device__ __noinline__ double coincident_rescan(const double2 *s_pos, const dou
             const double2 qj = s_mr[jj];
             const double md = ri + qj.y;
             const double f = qj.x / (md * md);   // m_j / mindsqr ; m_i*G applied by the caller
-            ax += (j > i) ? f : -f;
+            const bool j_is_higher = orig ? orig[j] > orig[i] : j > i;
+            ax += j_is_higher ? f : -f;
         }
     }
     return ax;

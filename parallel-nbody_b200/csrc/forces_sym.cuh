@@ -239,33 +239,40 @@ __device__ __forceinline__ int peek_acquire(const int *p)
     return v;
 }
 
-// Rare path, row side of a tile above the block (all j > i): + m_j / mindsqr for coincident j.
+// Rare path, row side of a tile above the block (all slots j > slot i): +- m_j / mindsqr for coincident j.  The
+// reference gives the body with the lower ORIGINAL index (+force, 0) (atan2(0,0) = 0, nbody-seq.c:91-106): in cell
+// order (orig != nullptr) the slot order says nothing about that for bodies that met after the last re-sort.
 __device__ __noinline__ double sym_row_rescan(const double2 *s_pos, const double2 *s_mr, int cnt, double xi, double yi,
-                                              double ri)
+                                              double ri, const int *orig, int jb, int i)
 {
     double ax = 0.0;
+    const int oi = orig ? orig[i] : 0;
     for (int jj = 0; jj < cnt; ++jj) {
         const double2 pj = s_pos[jj];
         if (pj.x == xi && pj.y == yi) {
             const double2 qj = s_mr[jj];
             const double md = ri + qj.y;
-            ax += qj.x / (md * md);
+            const double f = qj.x / (md * md);
+            ax += (!orig || orig[jb + jj] > oi) ? f : -f;
         }
     }
     return ax;
 }
 
-// Rare path, column side: sum over the block's bodies i (all < j) coincident with body j of m_i / mindsqr.
+// Rare path, column side: sum over the block's bodies i (slots below j) coincident with body j of +- m_i / mindsqr
+// (+: i has the lower original index, so j takes the reaction -force; the caller multiplies by -G m_j / 2).
 __device__ __noinline__ double sym_col_rescan(const double2 *pos, const double2 *mr, int i0, int i1, double xj,
-                                              double yj, double rj)
+                                              double yj, double rj, const int *orig, int j)
 {
     double c = 0.0;
+    const int oj = orig ? orig[j] : 0;
     for (int i = i0; i < i1; ++i) {
         const double2 pi = pos[i];
         if (pi.x == xj && pi.y == yj) {
             const double2 qi = mr[i];
             const double md = qi.y + rj;
-            c += qi.x / (md * md);
+            const double f = qi.x / (md * md);
+            c += (!orig || orig[i] < oj) ? f : -f;
         }
     }
     return c;
@@ -382,7 +389,8 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
 #pragma unroll
             for (int k = 0; k < SYM_IB; ++k) {
                 if (b[k].minhi == 0) {
-                    b[k].ax += 2.0 * coincident_rescan(tp, tm, cnt, jb, idx[k], b[k].x, b[k].y, b[k].r);
+                    if (idx[k] < a.n)
+                        b[k].ax += 2.0 * coincident_rescan(tp, tm, cnt, jb, idx[k], b[k].x, b[k].y, b[k].r, a.orig);
                     b[k].minhi = 0x7fffffff;
                 }
             }
@@ -425,7 +433,7 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
             for (int k = 0; k < SYM_IB; ++k) {
                 if (b[k].minhi == 0) {
                     if (idx[k] < a.n) {
-                        b[k].ax += 2.0 * sym_row_rescan(tp, tm, cnt, b[k].x, b[k].y, b[k].r);
+                        b[k].ax += 2.0 * sym_row_rescan(tp, tm, cnt, b[k].x, b[k].y, b[k].r, a.orig, jb, idx[k]);
                         hit = true;
                     }
                     b[k].minhi = 0x7fffffff;
@@ -444,7 +452,7 @@ __global__ void __launch_bounds__(SYM_THREADS, MINB) forces_sym_kernel(const Sym
                 }
                 const double2 pj = tp[jt];
                 const double2 qj = tm[jt];
-                if (s_flag[tile & 1]) cx += 2.0 * sym_col_rescan(a.pos, a.mr, i0, i1, pj.x, pj.y, qj.y);
+                if (s_flag[tile & 1]) cx += 2.0 * sym_col_rescan(a.pos, a.mr, i0, i1, pj.x, pj.y, qj.y, a.orig, jb + jt);
                 const double gmj = -NBODY_SYM_GH * qj.x;
                 s_seg[(jb - jc0) % SYM_SEG + jt] = make_double2(gmj * cx, gmj * cy);
             }

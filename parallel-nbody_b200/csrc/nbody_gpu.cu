@@ -445,6 +445,7 @@ static int enqueue_forces(nbody_gpu *h, Shard &s, int slot, double2 *exact_out)
         a.nseg = s.nseg;
         a.error_word = s.sym_err;
         a.boxes = s.boxes;
+        a.orig = h->sorted ? s.orig : nullptr;
         a.n = h->n;
         a.npad = h->npad;
         a.cm = h->cm;

@@ -79,6 +79,7 @@ struct SymArgs {
     int nseg;
     int *error_word;      // set to SYM_ERR_TURN when a CTA gave up waiting for its turn
     const double *boxes;  // [ceil(n/TILE_J)][8] per-tile bounding boxes (xmin ymin xmax ymax rmax . . .), or nullptr
+    const int *orig;      // cell order: slot -> original body index (decides the sign for coincident bodies), or nullptr
     int n;
     int npad;
     ChunkMap cm;
