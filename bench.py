@@ -175,7 +175,7 @@ def cpu_seq_sample(oracle_lib, b, n, budget_s):
     return 2.0 * ev / dt, rows2, dt
 
 
-def run_reference_binary(n, steps, timeout=900):
+def run_reference_binary(n, steps, timeout=900, threads_per_rank=1):
     """The reference's OWN parallel program (unmodified nbody-par.c built by oracle/Makefile against the
     fork/shared-memory MPI stand-in; MAXBODIES raised) on all host cores, pure MPI (one rank per core).
     Returns None if oracle/_ref/nbody-par-big is not built or the run fails."""
@@ -184,13 +184,14 @@ def run_reference_binary(n, steps, timeout=900):
         return None
     import tempfile
     import oracle_lib
-    cores = os.cpu_count() or 1
+    cores = max(1, (os.cpu_count() or 1) // threads_per_rank)   # ranks
+    hybrid = ["--openmp"] if threads_per_rank > 1 else []       # nbody-par.c:302,366,395: the OpenMP loops are opt-in
     with tempfile.TemporaryDirectory() as d:
         ppm = os.path.join(d, "nbody.ppm")
         oracle_lib.write_ppm(ppm, XDIM, YDIM)
-        env = dict(os.environ, MPISHIM_NP=str(cores), OMP_NUM_THREADS="1")
+        env = dict(os.environ, MPISHIM_NP=str(cores), OMP_NUM_THREADS=str(threads_per_rank))
         try:
-            r = subprocess.run([exe, str(n), "0", ppm, str(steps)], env=env, cwd=d, stdout=subprocess.DEVNULL,
+            r = subprocess.run([exe, str(n), "0", ppm, str(steps)] + hybrid, env=env, cwd=d, stdout=subprocess.DEVNULL,
                                stderr=subprocess.PIPE, text=True, timeout=timeout)
         except (OSError, subprocess.TimeoutExpired):
             return None
@@ -199,7 +200,7 @@ def run_reference_binary(n, steps, timeout=900):
         return None
     secs = float(took[0].split(":")[1].split()[0])
     return {"kind": "reference", "binary": "oracle/_ref/nbody-par-big (reference nbody-par.c + MPI stand-in)",
-            "ranks": cores, "threads_per_rank": 1, "n": n, "steps": steps, "seconds": secs,
+            "ranks": cores, "threads_per_rank": threads_per_rank, "openmp": bool(hybrid), "n": n, "steps": steps, "seconds": secs,
             "value": steps * n * (n - 1.0) / max(secs, 1e-9), "unit": UNIT}
 
 
@@ -265,6 +266,8 @@ def run_reference(args, rank, world):
 
     # the reference program itself: first at a size it finishes in seconds (predicts a full step), then ONE full step
     chk = reference_binary_check()
+    # north_star's "MPI+OpenMP" shape of the reference: cores/4 ranks x 4 threads with --openmp, at the small size
+    hybrid = run_reference_binary(16384, 2, timeout=300, threads_per_rank=4) if (chk and threads >= 4) else None
     full = None
     if chk and not args.no_reference_full_step:
         predicted = n * (n - 1.0) / chk["value"]
@@ -278,16 +281,22 @@ def run_reference(args, rank, world):
                          "raised, int overflows of the init fixed; built against a fork/shared-memory MPI stand-in), %d ranks x 1 "
                          "thread, its own 'N-body took' timer: %.1f s; --steps/--warmup apply to the port cross-check only"
                          % (n, threads, full["seconds"]),
-               "port_cross_check": port, "reference_check_small": chk}
-        note = "one real full step of the reference program; ms_per_step is that step"
+               "port_cross_check": dict(port, steps=args.steps, warmup=args.warmup), "reference_check_small": chk}
+        note = ("one real full step of the reference program; ms_per_step is that step; steps/warmup describe what was "
+                "timed (the requested --steps/--warmup drive the port cross-check only, see requested_steps)")
+        steps_timed, warmup_timed = 1, 0
     else:
         value, ms_per_step = port_value, dt / args.steps * 1e3 * (n / float(rows))
         cpu = dict(port)
         if chk:
             cpu["reference_check"] = chk
         note = "port sample (the reference binary is missing or a full step would exceed the limit); ms_per_step is the sample time scaled to a full step (x N/rows)"
+        steps_timed, warmup_timed = args.steps, args.warmup
+    if hybrid:
+        cpu["reference_check_hybrid"] = hybrid
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+            "steps": steps_timed, "warmup": warmup_timed, "requested_steps": args.steps, "requested_warmup": args.warmup,
+            "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": {"workload": workload + "; CPU: nbody-par MPI ranks on the host cores", "n": n,
                                             "mode": "reference", "parallelism": "%d host cores" % threads},
@@ -542,6 +551,56 @@ def main():
                   "what": "set_state(initial) + step(%d) + fetch on the %d-rank handle vs a one-GPU handle on the same device, "
                           "all six arrays, every rank (MIN-reduced)" % (k, world)}
 
+    # ---- more multi-rank parity (each against one GPU, bit for bit, MIN over ranks) and BASELINE config 5 -----------
+    def fresh_nccl_id():
+        idt = torch.zeros(nb.NCCL_ID_BYTES, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(nb.nccl_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        return bytes(idt.cpu().numpy().tobytes())
+
+    def sharded_against_one_gpu(arrays, k, timed_steps=0, **kw):
+        gs = nb.NBodyGPU(*arrays, xdim=XDIM, ydim=YDIM, mode=mode, device=local_rank, rank=rank, nranks=world,
+                         nccl_id=fresh_nccl_id(), **kw)
+        out = {}
+        if timed_steps:
+            gs.step(2)
+            gs.sync()
+            barrier()
+            ms = maxreduce(gs.step_bench(timed_steps, flush_l2=True))
+            nn = len(arrays[0])
+            out.update({"steps": timed_steps, "ms_per_step": ms / timed_steps,
+                        "pair_interactions_per_s": timed_steps * nn * (nn - 1.0) / (ms * 1e-3)})
+            gs.set_state(*arrays[:4])
+        gs.step(k)
+        sharded = gs.fetch()
+        d = gs.describe()
+        gs.close()
+        g1 = nb.NBodyGPU(*arrays, xdim=XDIM, ydim=YDIM, mode=mode, device=local_rank,
+                         **{a: v for a, v in kw.items() if a != "p2p"})
+        g1.step(k)
+        single = g1.fetch()
+        g1.close()
+        same = all(np.array_equal(a.view(np.uint64), c.view(np.uint64)) for a, c in zip(sharded, single))
+        flag = torch.tensor([1 if same else 0], dtype=torch.int64, device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        out["parity"] = {"bits_equal_to_1gpu": bool(flag.item()), "steps": k, "ranks_checked": world,
+                         "sha256": state_sha256(sharded), "exchange": d.get("exchange"), "sorts": d.get("sorts")}
+        return out
+
+    c5 = None
+    if world > 1 and not args.no_parity:
+        init = (bx, by, bxv, byv, bmass, bradius)
+        # a run that crosses re-sorts of the cell order (sort_interval = 2: sorts before steps 2 and 4)
+        parity["across_resorts"] = dict(sharded_against_one_gpu(init, 5, sort_interval=2)["parity"], sort_interval=2)
+        # the same step over the ncclAllGather exchange instead of the peer-memory stores
+        parity["nccl_exchange"] = dict(sharded_against_one_gpu(init, 3, p2p=-1)["parity"], p2p=-1)
+        if world == 8 and n == N_DEFAULT and not args.no_configs:
+            n5 = 1048576   # BASELINE config 5: N = 1 048 576 x 10 steps on 8 GPUs (nbody-par.c:901-921 is the loop)
+            c5 = sharded_against_one_gpu(nb.reference_init(n5, XDIM, YDIM), 3, timed_steps=10)
+            c5["kernel"] = "forces_sym_kernel<64,8>"
+            c5["timing"] = "nbody_gpu_step_bench(10) on the 8-rank handle, CUDA-graph path, L2 flushed per launch, max over ranks"
+
     desc = g.describe()
     far = g.far_fraction() if desc.get("cell_order") else 0.0
     if rank != 0:
@@ -602,8 +661,8 @@ def main():
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": t_ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "BASELINE config 4: N=%d bodies, reference initialiser (srand 27102015), world %dx%d, "
-                                   "%s mode, row blocks sharded over %d GPU(s), per-step exchange: %s"
+            "config": {"workload": "BASELINE config 4: N=%d bodies, reference initialiser (srand 27102015), world %dx%d; "
+                                   "GPU: %s mode, row blocks sharded over %d GPU(s), per-step exchange: %s"
                                    % (n, XDIM, YDIM, args.mode, world, desc.get("exchange", "none")),
                        "n": n, "mode": args.mode, "parallelism": "row-shard x%d" % world,
                        "step_path": "CUDA graph of %d steps per launch" % desc["graph_steps"] if desc.get("graph_steps") else "plain launches",
@@ -625,6 +684,8 @@ def main():
         line["cpu_baseline"] = cpu
     if configs:
         line["configs"] = configs
+    if c5:
+        line.setdefault("configs", {})["c5_1048576x10"] = c5
     print(json.dumps(line), flush=True)
     g.close()
     if dist is not None:
