@@ -13,27 +13,38 @@
 
 namespace nbody {
 
-constexpr int EXW_ROWS = 32;                       // bodies i per CTA
+constexpr int EXW_ROWS = 32;                       // bodies i per CTA (the wide shape); 16 when the launch is small
 constexpr int EXW_CWARPS = 16;                     // compute warps
 constexpr int EXW_THREADS = (EXW_CWARPS + 1) * 32; // + 1 fold warp
 constexpr int EXW_TJ = 64;                         // bodies j per tile
 constexpr int EXW_JPW = EXW_TJ / EXW_CWARPS;       // j's per compute warp per tile
-constexpr int EXW_SMEM_BYTES = 2 * EXW_TJ * 16 * 2 /* pos, mr */ + 2 * EXW_TJ * 32 * 16 /* terms */ +
-                               NBODY_DM_ATAN_TAB_LEN * 8 + 64;
+constexpr int exw_smem_bytes(int rows)
+{
+    return 2 * EXW_TJ * 16 * 2 /* pos, mr */ + 2 * EXW_TJ * rows * 16 /* terms */ + NBODY_DM_ATAN_TAB_LEN * 8 + 64;
+}
 
+// ROWS = 32: lane = body, a warp instruction evaluates one j for 32 bodies.  ROWS = 16: half as many bodies per
+// CTA and twice as many CTAs -- for launches that would otherwise leave SMs empty (N = 4096: 128 CTAs on 148 SMs) --
+// with lanes 0..15 and 16..31 working on two different j's for the same 16 bodies.  Which j a lane evaluates does
+// not matter: every term lands in its (j, body) slot and the fold warp adds them in j order either way: same bits.
+template <int ROWS>
 __global__ void __launch_bounds__(EXW_THREADS) forces_exact_wide_kernel(const ForceArgs a)
 {
+    static_assert(ROWS == 32 || ROWS == 16, "lane = body, or two j's per warp instruction");
+    constexpr int JPI = 32 / ROWS;                 // j's per warp instruction
     extern __shared__ __align__(128) unsigned char exw_smem[];
     double2 *s_pos = reinterpret_cast<double2 *>(exw_smem);      // [2][EXW_TJ]
     double2 *s_mr = s_pos + 2 * EXW_TJ;                          // [2][EXW_TJ]
-    double2 *s_term = s_mr + 2 * EXW_TJ;                         // [2][EXW_TJ][32]
-    double *s_tab = reinterpret_cast<double *>(s_term + 2 * EXW_TJ * 32);
+    double2 *s_term = s_mr + 2 * EXW_TJ;                         // [2][EXW_TJ][ROWS]
+    double *s_tab = reinterpret_cast<double *>(s_term + 2 * EXW_TJ * ROWS);
     uint64_t *s_full = reinterpret_cast<uint64_t *>(s_tab + NBODY_DM_ATAN_TAB_LEN);
 
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int warp = tid >> 5;
-    const int i = a.lo + blockIdx.x * EXW_ROWS + lane;
+    const int row = lane % ROWS;                  // body of this lane
+    const int sub = lane / ROWS;                  // which of the JPI j's of a warp instruction
+    const int i = a.lo + blockIdx.x * ROWS + row;
     const bool live = i < a.hi;
     const int ntiles = (a.n + EXW_TJ - 1) / EXW_TJ;
 
@@ -74,10 +85,10 @@ __global__ void __launch_bounds__(EXW_THREADS) forces_exact_wide_kernel(const Fo
                 mbar_wait(&s_full[st], (t >> 1) & 1);
                 const int jb = t * EXW_TJ;
                 const int cnt = min(EXW_TJ, a.n - jb);
-                double2 *term = s_term + st * EXW_TJ * 32;
+                double2 *term = s_term + st * EXW_TJ * ROWS;
 #pragma unroll
-                for (int u = 0; u < EXW_JPW; ++u) {
-                    const int jj = warp + u * EXW_CWARPS;
+                for (int u = 0; u < EXW_JPW / JPI; ++u) {
+                    const int jj = warp + (u * JPI + sub) * EXW_CWARPS;
                     if (jj < cnt) {
                         const int j = jb + jj;
                         const double2 pj = s_pos[st * EXW_TJ + jj];
@@ -90,17 +101,17 @@ __global__ void __launch_bounds__(EXW_THREADS) forces_exact_wide_kernel(const Fo
                         // XF(c) -= xf for j < i, XF(b) += xf for j > i (negation is exact); the self term is +0
                         double2 v = make_double2(lower ? -fx : fx, lower ? -fy : fy);
                         if (j == i) v = make_double2(0.0, 0.0);
-                        term[jj * 32 + lane] = v;
+                        term[jj * ROWS + row] = v;
                     }
                 }
             }
         } else if (t > 0) {
             const int tp = t - 1;
             const int cnt = min(EXW_TJ, a.n - tp * EXW_TJ);
-            const double2 *term = s_term + (tp & 1) * EXW_TJ * 32;
+            const double2 *term = s_term + (tp & 1) * EXW_TJ * ROWS;
 #pragma unroll 8
             for (int jj = 0; jj < cnt; ++jj) {
-                const double2 v = term[jj * 32 + lane];
+                const double2 v = term[jj * ROWS + row];   // ROWS = 16: lanes 16..31 fold the same bodies again, unused
                 ax = __dadd_rn(ax, v.x);
                 ay = __dadd_rn(ay, v.y);
             }
@@ -110,7 +121,7 @@ __global__ void __launch_bounds__(EXW_THREADS) forces_exact_wide_kernel(const Fo
         if (tid == 0 && t + 2 < ntiles) issue(t + 2);
     }
 
-    if (warp == EXW_CWARPS && live) a.out[i] = make_double2(ax, ay);
+    if (warp == EXW_CWARPS && sub == 0 && live) a.out[i] = make_double2(ax, ay);
 }
 
 }  // namespace nbody

@@ -28,11 +28,18 @@ int launch_forces_exact(const ForceArgs &a, cudaStream_t st)
     cudaGetDevice(&dev);
     bool &attr_set = attr_set_dev[dev & 63];
     if (!attr_set) {
-        const cudaError_t e = cudaFuncSetAttribute(forces_exact_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EXW_SMEM_BYTES);
+        cudaError_t e = cudaFuncSetAttribute(forces_exact_wide_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, exw_smem_bytes(32));
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(forces_exact_wide_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, exw_smem_bytes(16));
         if (e != cudaSuccess) return static_cast<int>(e);
         attr_set = true;
     }
-    forces_exact_wide_kernel<<<(rows + EXW_ROWS - 1) / EXW_ROWS, EXW_THREADS, EXW_SMEM_BYTES, st>>>(a);
+    // 16 bodies per CTA while 32 would not even give every SM (148 on a B200) two CTAs: N = 4096 launches 256 CTAs
+    // instead of 128.  The choice cannot change a bit (see the kernel), so it may depend on the shard size.
+    if ((rows + EXW_ROWS - 1) / EXW_ROWS < 2 * 148)
+        forces_exact_wide_kernel<16><<<(rows + 15) / 16, EXW_THREADS, exw_smem_bytes(16), st>>>(a);
+    else
+        forces_exact_wide_kernel<32><<<(rows + 31) / 32, EXW_THREADS, exw_smem_bytes(32), st>>>(a);
     return 0;
 }
 
